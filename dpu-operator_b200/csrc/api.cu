@@ -1,0 +1,806 @@
+// api.cu — the C ABI of libb200sfc.so (include/b200sfc.h): rule staging, image commit,
+// kernel launches and the synthetic-traffic generator.  No CPU classification path exists in
+// this library; without a CUDA device sfc_create fails.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <errno.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/b200sfc.h"
+#include "classify.cuh"
+#include "gen.h"
+#include "tables.h"
+
+using namespace sfc;
+
+namespace {
+constexpr int kTile = 128;
+constexpr int kStages = 4;
+constexpr size_t kHostChunk = 1u << 18;  // packets per pipelined chunk in sfc_classify_host
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+}  // namespace
+
+struct sfc_handle {
+    int device = 0;
+    int sm_count = 0;
+    std::string err;
+    RuleStore rs;
+    // committed image
+    uint8_t* d_image = nullptr;
+    size_t image_bytes = 0;
+    uint64_t epoch = 0;
+    DevTables T{};
+    unsigned long long* d_counters = nullptr;
+    uint64_t launches = 0;
+    EncodeTiledFn encode = nullptr;
+    int ctas_per_sm[4] = {0, 0, 0, 0};
+    // sfc_classify_host staging
+    cudaStream_t hs[2] = {nullptr, nullptr};
+    cudaEvent_t ev[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+    uint8_t* d_hdr[2] = {nullptr, nullptr};
+    uint16_t* d_port[2] = {nullptr, nullptr};
+    uint64_t* d_res[2] = {nullptr, nullptr};
+    float last_kernel_ms = -1.f;
+    // offline handles (device_ordinal -1): rule staging and image building only, no CUDA calls
+    std::vector<uint8_t> host_image;
+    bool offline() const { return device < 0; }
+};
+
+namespace {
+
+int fail(sfc_handle* h, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (h) h->err = buf;
+    return code;
+}
+#define CUDA_TRY(h, expr)                                                                        \
+    do {                                                                                         \
+        cudaError_t e_ = (expr);                                                                 \
+        if (e_ != cudaSuccess) return fail(h, -EIO, "%s: %s", #expr, cudaGetErrorString(e_));    \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        if (dev < 0) return;
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+void bind_tables(sfc_handle* h) {
+    ImageHeader H;
+    cudaMemcpy(&H, h->d_image, sizeof(H), cudaMemcpyDeviceToHost);
+    DevTables& T = h->T;
+    const uint8_t* b = h->d_image;
+    T.flow4 = (const uint32_t*)(b + H.flow4_off);
+    T.flow6 = (const uint32_t*)(b + H.flow6_off);
+    T.flow4_seed = H.flow4_seed;
+    T.flow6_seed = H.flow6_seed;
+    T.flow4_nbuckets = H.flow4_nbuckets;
+    T.flow4_nhash = H.flow4_nhash;
+    T.flow4_count = H.flow4_count;
+    T.flow6_nbuckets = H.flow6_nbuckets;
+    T.flow6_nhash = H.flow6_nhash;
+    T.flow6_count = H.flow6_count;
+    T.l2x = (const L2Entry*)(b + H.l2x_off);
+    T.l2x_mask = H.l2x_mask;
+    T.l2x_count = H.l2x_count;
+    T.l2w = (const L2Wild*)(b + H.l2w_off);
+    T.l2w_n = H.l2w_n;
+    T.l2w_count = H.l2w_count;
+    T.nf = b + H.nf_off;
+    T.nf_n = H.nf_n;
+    T.lpm4_root = (const uint32_t*)(b + H.lpm4_root_off);
+    T.lpm4_nodes = (const uint32_t*)(b + H.lpm4_nodes_off);
+    T.lpm4_nh = (const uint16_t*)(b + H.lpm4_nh_off);
+    T.lpm4_count = H.lpm4_count;
+    T.lpm6_root = (const uint32_t*)(b + H.lpm6_root_off);
+    T.lpm6_nodes = (const uint32_t*)(b + H.lpm6_nodes_off);
+    T.lpm6_nh = (const uint16_t*)(b + H.lpm6_nh_off);
+    T.lpm6_count = H.lpm6_count;
+    T.acl_bv = (const uint32_t*)(b + H.acl_bv_off);
+    T.acl_base = (const uint32_t*)(b + H.acl_base_off);
+    T.acl_rule = (const uint32_t*)(b + H.acl_rule_off);
+    T.acl_nrules = H.acl_nrules;
+    T.acl_nwords = H.acl_nwords;
+    T.acl_npos4 = H.acl_npos4;
+    T.acl_npos6 = H.acl_npos6;
+    memcpy(T.acl_pos4, H.acl_pos4, kAclMaxPos);
+    memcpy(T.acl_pos6, H.acl_pos6, kAclMaxPos);
+    memcpy(T.acl_slot4, H.acl_slot4, kAclMaxPos);
+    memcpy(T.acl_slot6, H.acl_slot6, kAclMaxPos);
+    T.counters = h->d_counters;
+    h->epoch = H.epoch;
+}
+
+int install_image_from_host(sfc_handle* h, const uint8_t* img, size_t len) {
+    uint8_t* d = nullptr;
+    CUDA_TRY(h, cudaMalloc(&d, len));
+    cudaError_t e = cudaMemcpy(d, img, len, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        cudaFree(d);
+        return fail(h, -EIO, "image upload: %s", cudaGetErrorString(e));
+    }
+    CUDA_TRY(h, cudaDeviceSynchronize());
+    if (h->d_image) cudaFree(h->d_image);
+    h->d_image = d;
+    h->image_bytes = len;
+    bind_tables(h);
+    return 0;
+}
+
+template <bool C, bool A>
+auto kernel_ptr() {
+    return classify_kernel<kTile, kStages, C, A>;
+}
+
+template <bool C, bool A>
+int launch_variant(sfc_handle* h, int variant, const CUtensorMap& map, const uint16_t* in_port, uint64_t* result,
+                   size_t n, cudaStream_t st) {
+    auto kern = kernel_ptr<C, A>();
+    constexpr int smem = SmemLayout<kTile, kStages>::kBytes;
+    if (!h->ctas_per_sm[variant]) {
+        CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        int per = 0;
+        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, kern, kTile + 32, smem));
+        if (per < 1) return fail(h, -EIO, "classify kernel does not fit on an SM");
+        h->ctas_per_sm[variant] = per;
+    }
+    uint64_t n_tiles = (n + kTile - 1) / kTile;
+    uint64_t grid = std::min<uint64_t>(n_tiles, (uint64_t)h->sm_count * h->ctas_per_sm[variant]);
+    kern<<<(unsigned)grid, kTile + 32, smem, st>>>(map, in_port, result, (uint64_t)n, (uint32_t)n_tiles, h->T);
+    CUDA_TRY(h, cudaGetLastError());
+    ++h->launches;
+    return 0;
+}
+
+int launch_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
+                    uint32_t flags, cudaStream_t st) {
+    if (!h->d_image) return fail(h, -EINVAL, "sfc_classify: no committed table image (call sfc_commit)");
+    if (((uintptr_t)hdr & 15) != 0) return fail(h, -EINVAL, "sfc_classify: hdr must be 16-byte aligned");
+    if (n > (1ull << 31)) return fail(h, -EINVAL, "sfc_classify: at most 2^31 packets per call");
+    CUtensorMap map;
+    cuuint64_t dims[2] = {16, (cuuint64_t)n};  // 16 x u32 per record, n records
+    cuuint64_t strides[1] = {64};
+    cuuint32_t box[2] = {16, (cuuint32_t)kTile};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = h->encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(hdr), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(h, -EIO, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    bool c = flags & SFC_F_COUNTERS, a = h->T.acl_nrules > 0;
+    if (c && a) return launch_variant<true, true>(h, 3, map, in_port, result, n, st);
+    if (c) return launch_variant<true, false>(h, 2, map, in_port, result, n, st);
+    if (a) return launch_variant<false, true>(h, 1, map, in_port, result, n, st);
+    return launch_variant<false, false>(h, 0, map, in_port, result, n, st);
+}
+
+__global__ void gen_kernel(sfc_gen_spec spec, uint64_t first, uint64_t n, uint8_t* hdr, uint16_t* in_port) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint8_t h[64];
+    uint16_t port;
+    gen_packet(spec, first + i, h, port);
+    uint4* dst = reinterpret_cast<uint4*>(hdr + i * 64);
+    const uint4* src = reinterpret_cast<const uint4*>(h);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) dst[k] = src[k];
+    in_port[i] = port;
+}
+
+}  // namespace
+
+// =================================================================== life cycle ==========
+extern "C" {
+
+const char* sfc_version(void) { return "b200sfc 0.1 (image v3)"; }
+
+int sfc_create(int device_ordinal, sfc_handle** out) {
+    if (!out) return -EINVAL;
+    *out = nullptr;
+    if (device_ordinal == -1) {  // offline: stage rules and build images, nothing else
+        sfc_handle* h = new sfc_handle();
+        h->device = -1;
+        *out = h;
+        return 0;
+    }
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return -ENODEV;
+    if (device_ordinal < 0 || device_ordinal >= count) return -ENODEV;
+    sfc_handle* h = new sfc_handle();
+    h->device = device_ordinal;
+    DeviceGuard g(device_ordinal);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device_ordinal) != cudaSuccess || prop.major < 10) {
+        delete h;
+        return -ENODEV;  // sm_100a code only
+    }
+    h->sm_count = prop.multiProcessorCount;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn) {
+        delete h;
+        return -ENOSYS;
+    }
+    h->encode = (EncodeTiledFn)fn;
+    if (cudaMalloc(&h->d_counters, SFC_CNT_TOTAL * sizeof(uint64_t)) != cudaSuccess ||
+        cudaMemset(h->d_counters, 0, SFC_CNT_TOTAL * sizeof(uint64_t)) != cudaSuccess) {
+        delete h;
+        return -ENOMEM;
+    }
+    *out = h;
+    return 0;
+}
+
+int sfc_destroy(sfc_handle* h) {
+    if (!h) return -EINVAL;
+    if (h->offline()) {
+        delete h;
+        return 0;
+    }
+    DeviceGuard g(h->device);
+    cudaDeviceSynchronize();
+    if (h->d_image) cudaFree(h->d_image);
+    if (h->d_counters) cudaFree(h->d_counters);
+    for (int i = 0; i < 2; ++i) {
+        if (h->d_hdr[i]) cudaFree(h->d_hdr[i]);
+        if (h->d_port[i]) cudaFree(h->d_port[i]);
+        if (h->d_res[i]) cudaFree(h->d_res[i]);
+        if (h->hs[i]) cudaStreamDestroy(h->hs[i]);
+        for (int j = 0; j < 2; ++j)
+            if (h->ev[i][j]) cudaEventDestroy(h->ev[i][j]);
+    }
+    delete h;
+    return 0;
+}
+
+const char* sfc_last_error(const sfc_handle* h) { return h ? h->err.c_str() : "null handle"; }
+
+int sfc_set_option(sfc_handle* h, const char* name, long value) {
+    if (!h || !name) return -EINVAL;
+    if (!strcmp(name, "flow_load_pct")) {
+        if (value < 5 || value > 90) return fail(h, -EINVAL, "flow_load_pct must be 5..90");
+        h->rs.flow_load_pct = (int)value;
+        return 0;
+    }
+    if (!strcmp(name, "flow_hashes")) {
+        if (value < 2 || value > kMaxHashes) return fail(h, -EINVAL, "flow_hashes must be 2 or 3");
+        h->rs.flow_hashes = (int)value;
+        return 0;
+    }
+    return fail(h, -ENOENT, "unknown option '%s'", name);
+}
+
+// =================================================================== ports ===============
+int sfc_port_add(sfc_handle* h, const char* name, uint16_t* port_id) {
+    if (!h || !name || !*name) return h ? fail(h, -EINVAL, "sfc_port_add: empty name") : -EINVAL;
+    auto it = h->rs.port_by_name.find(name);
+    if (it != h->rs.port_by_name.end()) {
+        if (port_id) *port_id = it->second;
+        return 0;
+    }
+    size_t id = 0;
+    while (id < h->rs.port_names.size() && !h->rs.port_names[id].empty()) ++id;
+    if (id >= SFC_MAX_PORTS) return fail(h, -ENOSPC, "sfc_port_add: all %u port ids are in use", SFC_MAX_PORTS);
+    if (id == h->rs.port_names.size()) h->rs.port_names.emplace_back();
+    h->rs.port_names[id] = name;
+    h->rs.port_by_name[name] = (uint16_t)id;
+    if (port_id) *port_id = (uint16_t)id;
+    return 0;
+}
+
+int sfc_port_del(sfc_handle* h, const char* name) {
+    if (!h || !name) return -EINVAL;
+    auto it = h->rs.port_by_name.find(name);
+    if (it == h->rs.port_by_name.end()) return fail(h, -ENOENT, "sfc_port_del: no port named '%s'", name);
+    h->rs.port_names[it->second].clear();
+    h->rs.port_by_name.erase(it);
+    return 0;
+}
+
+int sfc_port_lookup(const sfc_handle* h, const char* name, uint16_t* port_id) {
+    if (!h || !name) return -EINVAL;
+    auto it = h->rs.port_by_name.find(name);
+    if (it == h->rs.port_by_name.end()) return -ENOENT;
+    if (port_id) *port_id = it->second;
+    return 0;
+}
+
+long sfc_port_list(const sfc_handle* h, char* buf, size_t len) {
+    if (!h) return -EINVAL;
+    std::string s;
+    for (auto& n : h->rs.port_names)
+        if (!n.empty()) {
+            s += n;
+            s += '\n';
+        }
+    if (buf && len) {
+        size_t c = std::min(len - 1, s.size());
+        memcpy(buf, s.data(), c);
+        buf[c] = 0;
+    }
+    return (long)s.size() + 1;
+}
+
+// =================================================================== L2 steering =========
+int sfc_l2_rule_add(sfc_handle* h, uint16_t in_port, uint16_t out_port, const uint8_t* dst_mac, uint32_t* rule_id) {
+    if (!h) return -EINVAL;
+    if (in_port >= SFC_MAX_PORTS || out_port >= SFC_MAX_PORTS)
+        return fail(h, -EINVAL, "sfc_l2_rule_add: port id out of range");
+    L2Rule r{};
+    r.in_port = in_port;
+    r.out_port = out_port;
+    r.has_mac = dst_mac != nullptr;
+    if (dst_mac) memcpy(r.mac, dst_mac, 6);
+    // priorities exactly as ovs-dp/ovsdp.go:120,127,135 writes them
+    r.priority = !dst_mac ? 10u : (in_port == out_port ? 100u : 32768u);
+    for (auto& e : h->rs.l2)
+        if (e.in_port == r.in_port && e.has_mac == r.has_mac && e.priority == r.priority &&
+            (!r.has_mac || !memcmp(e.mac, r.mac, 6))) {
+            e.out_port = out_port;  // add-flow on an identical match replaces the actions
+            if (rule_id) *rule_id = e.id;
+            return 0;
+        }
+    if (h->rs.next_l2_id >= (1u << 28)) return fail(h, -ENOSPC, "sfc_l2_rule_add: rule ids exhausted");
+    r.id = h->rs.next_l2_id++;
+    h->rs.l2.push_back(r);
+    if (rule_id) *rule_id = r.id;
+    return 0;
+}
+
+int sfc_l2_rule_del(sfc_handle* h, uint16_t in_port, const uint8_t* dst_mac) {
+    if (!h) return -EINVAL;
+    auto& v = h->rs.l2;
+    v.erase(std::remove_if(v.begin(), v.end(),
+                           [&](const L2Rule& e) {
+                               if (e.in_port != in_port) return false;
+                               if (!dst_mac) return true;  // loose delete: every flow with this in_port
+                               return e.has_mac && !memcmp(e.mac, dst_mac, 6);
+                           }),
+            v.end());
+    return 0;
+}
+
+int sfc_chain_set(sfc_handle* h, const uint16_t* nf_in_ports, const uint16_t* nf_out_ports, size_t n_nfs) {
+    if (!h) return -EINVAL;
+    if (n_nfs > SFC_MAX_NFS) return fail(h, -EINVAL, "sfc_chain_set: at most %u network functions", SFC_MAX_NFS);
+    if (n_nfs && (!nf_in_ports || !nf_out_ports)) return fail(h, -EINVAL, "sfc_chain_set: null port array");
+    for (size_t i = 0; i < n_nfs; ++i)
+        if (nf_in_ports[i] >= SFC_MAX_PORTS || nf_out_ports[i] >= SFC_MAX_PORTS)
+            return fail(h, -EINVAL, "sfc_chain_set: port id out of range");
+    h->rs.nf_in.assign(nf_in_ports, nf_in_ports + n_nfs);
+    h->rs.nf_out.assign(nf_out_ports, nf_out_ports + n_nfs);
+    return 0;
+}
+
+// =================================================================== flows ===============
+int sfc_flow_add_bulk(sfc_handle* h, const sfc_flow_key* keys, const sfc_flow_action* acts, size_t n,
+                      uint32_t* first_id) {
+    if (!h || (n && (!keys || !acts))) return -EINVAL;
+    RuleStore& rs = h->rs;
+    if ((uint64_t)rs.next_flow_id + n > SFC_MAX_FLOWS) return fail(h, -ENOSPC, "flow ids exhausted");
+    size_t before = rs.flows.size();
+    uint32_t id0 = rs.next_flow_id;
+    if (n > 4096) rs.flows.reserve(before + n);
+    std::string err;
+    for (size_t i = 0; i < n; ++i) {
+        FlowRec f;
+        int code = 0;
+        if (!flow_from_key(keys[i], acts[i], f, err)) code = -EINVAL;
+        else if (rs.flow_index.find(rs.flows, f) >= 0) {
+            err = "flow already present";
+            code = -EEXIST;
+        }
+        if (code) {  // roll the whole batch back
+            rs.flows.resize(before);
+            rs.flow_index.rebuild(rs.flows, before);
+            return fail(h, code, "sfc_flow_add: entry %zu: %s", i, err.c_str());
+        }
+        f.id = id0 + (uint32_t)i;
+        rs.flows.push_back(f);
+        rs.flow_index.insert(rs.flows, (uint32_t)(rs.flows.size() - 1));
+    }
+    rs.next_flow_id = id0 + (uint32_t)n;
+    if (first_id) *first_id = id0;
+    return 0;
+}
+
+int sfc_flow_add(sfc_handle* h, const sfc_flow_key* key, const sfc_flow_action* act, uint32_t* flow_id) {
+    return sfc_flow_add_bulk(h, key, act, 1, flow_id);
+}
+
+int sfc_flow_del(sfc_handle* h, const sfc_flow_key* key) {
+    if (!h || !key) return -EINVAL;
+    FlowRec f;
+    std::string err;
+    sfc_flow_action a{SFC_ACT_TO_CP, 0, 0};
+    if (!flow_from_key(*key, a, f, err)) return fail(h, -EINVAL, "sfc_flow_del: %s", err.c_str());
+    int64_t pos = h->rs.flow_index.find(h->rs.flows, f);
+    if (pos < 0) return fail(h, -ENOENT, "sfc_flow_del: no such flow");
+    h->rs.flows[pos] = h->rs.flows.back();
+    h->rs.flows.pop_back();
+    h->rs.flow_index.rebuild(h->rs.flows, h->rs.flows.size());
+    return 0;
+}
+
+// =================================================================== LPM =================
+static int lpm_words(sfc_handle* h, int af, const uint8_t* prefix, int len, uint32_t* w) {
+    if (af != 4 && af != 6) return fail(h, -EINVAL, "lpm: af must be 4 or 6");
+    if (!prefix || len < 0 || len > (af == 4 ? 32 : 128)) return fail(h, -EINVAL, "lpm: bad prefix length");
+    for (int k = 0; k < 4; ++k) {
+        uint32_t v = 0;
+        if (af == 6 || k == 0)
+            v = ((uint32_t)prefix[4 * k] << 24) | ((uint32_t)prefix[4 * k + 1] << 16) |
+                ((uint32_t)prefix[4 * k + 2] << 8) | prefix[4 * k + 3];
+        w[k] = v & mask32(len - 32 * k);
+    }
+    return 0;
+}
+
+int sfc_lpm_add(sfc_handle* h, int af, const uint8_t* prefix, int len, uint16_t out_port, uint32_t* prefix_id) {
+    if (!h) return -EINVAL;
+    LpmRec r{};
+    int rc = lpm_words(h, af, prefix, len, r.w);
+    if (rc) return rc;
+    if (out_port >= SFC_MAX_PORTS) return fail(h, -EINVAL, "sfc_lpm_add: out_port out of range");
+    auto& v = af == 4 ? h->rs.lpm4 : h->rs.lpm6;
+    RuleStore::LpmKey key = {(uint32_t)len, r.w[0], r.w[1], r.w[2], r.w[3]};
+    auto it = v.find(key);
+    if (it != v.end()) {  // same prefix again: replace the next hop, keep the id
+        it->second.out_port = out_port;
+        if (prefix_id) *prefix_id = it->second.id;
+        return 0;
+    }
+    if (h->rs.next_lpm_id >= (1u << 28)) return fail(h, -ENOSPC, "sfc_lpm_add: prefix ids exhausted");
+    r.len = len;
+    r.out_port = out_port;
+    r.id = h->rs.next_lpm_id++;
+    v[key] = r;
+    if (prefix_id) *prefix_id = r.id;
+    return 0;
+}
+
+int sfc_lpm_del(sfc_handle* h, int af, const uint8_t* prefix, int len) {
+    if (!h) return -EINVAL;
+    uint32_t w[4];
+    int rc = lpm_words(h, af, prefix, len, w);
+    if (rc) return rc;
+    auto& v = af == 4 ? h->rs.lpm4 : h->rs.lpm6;
+    RuleStore::LpmKey key = {(uint32_t)len, w[0], w[1], w[2], w[3]};
+    if (!v.erase(key)) return fail(h, -ENOENT, "sfc_lpm_del: no such prefix");
+    return 0;
+}
+
+// =================================================================== ACL =================
+int sfc_acl_add(sfc_handle* h, const sfc_acl_rule* rule, uint32_t* rule_id) {
+    if (!h || !rule) return -EINVAL;
+    if (h->rs.acl.size() >= SFC_MAX_ACL_RULES) return fail(h, -ENOSPC, "sfc_acl_add: table full");
+    if (h->rs.next_acl_id >= SFC_MAX_ACL_RULES) return fail(h, -ENOSPC, "sfc_acl_add: rule ids exhausted (sfc_clear)");
+    if (rule->ip_ver != 0 && rule->ip_ver != 4 && rule->ip_ver != 6) return fail(h, -EINVAL, "sfc_acl_add: ip_ver");
+    if (rule->verdict > SFC_ACL_DENY) return fail(h, -EINVAL, "sfc_acl_add: verdict");
+    for (int i = 0; i < 16; ++i) {
+        bool m = rule->src_mask[i] || rule->dst_mask[i];
+        if (m && rule->ip_ver == 0) return fail(h, -EINVAL, "sfc_acl_add: address mask needs ip_ver 4 or 6");
+        if (m && rule->ip_ver == 4 && i >= 4) return fail(h, -EINVAL, "sfc_acl_add: IPv4 mask bytes 4..15 must be 0");
+    }
+    AclRec a;
+    a.r = *rule;
+    a.id = h->rs.next_acl_id++;
+    h->rs.acl.push_back(a);
+    if (rule_id) *rule_id = a.id;
+    return 0;
+}
+
+int sfc_acl_del(sfc_handle* h, uint32_t rule_id) {
+    if (!h) return -EINVAL;
+    for (size_t i = 0; i < h->rs.acl.size(); ++i)
+        if (h->rs.acl[i].id == rule_id) {
+            h->rs.acl.erase(h->rs.acl.begin() + i);
+            return 0;
+        }
+    return fail(h, -ENOENT, "sfc_acl_del: no rule with id %u", rule_id);
+}
+
+int sfc_clear(sfc_handle* h) {
+    if (!h) return -EINVAL;
+    h->rs.clear_rules();
+    return 0;
+}
+
+// =================================================================== commit / image ======
+int sfc_commit(sfc_handle* h) {
+    if (!h) return -EINVAL;
+    DeviceGuard g(h->device);
+    std::vector<uint8_t> img;
+    std::string err;
+    if (!build_image(h->rs, h->epoch + 1, img, err)) return fail(h, -ENOSPC, "sfc_commit: %s", err.c_str());
+    if (h->offline()) {
+        h->host_image.swap(img);
+        h->image_bytes = h->host_image.size();
+        ++h->epoch;
+        return 0;
+    }
+    return install_image_from_host(h, img.data(), img.size());
+}
+
+size_t sfc_table_size(const sfc_handle* h) { return h ? h->image_bytes : 0; }
+uint64_t sfc_table_epoch(const sfc_handle* h) { return h ? h->epoch : 0; }
+
+int sfc_table_export(const sfc_handle* hc, void* buf, size_t len) {
+    sfc_handle* h = const_cast<sfc_handle*>(hc);
+    if (!h || !buf) return -EINVAL;
+    if (h->offline()) {
+        if (h->host_image.empty()) return fail(h, -ENOENT, "sfc_table_export: nothing committed");
+        if (len < h->host_image.size()) return fail(h, -ENOSPC, "sfc_table_export: buffer too small");
+        memcpy(buf, h->host_image.data(), h->host_image.size());
+        return 0;
+    }
+    if (!h->d_image) return fail(h, -ENOENT, "sfc_table_export: nothing committed");
+    if (len < h->image_bytes) return fail(h, -ENOSPC, "sfc_table_export: buffer too small");
+    DeviceGuard g(h->device);
+    CUDA_TRY(h, cudaMemcpy(buf, h->d_image, h->image_bytes, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int sfc_table_import(sfc_handle* h, const void* buf, size_t len) {
+    if (!h || !buf) return -EINVAL;
+    std::string err;
+    if (!validate_image((const uint8_t*)buf, len, err)) return fail(h, -EINVAL, "sfc_table_import: %s", err.c_str());
+    if (h->offline()) {
+        h->host_image.assign((const uint8_t*)buf, (const uint8_t*)buf + len);
+        h->image_bytes = len;
+        ImageHeader H;
+        memcpy(&H, buf, sizeof(H));
+        h->epoch = H.epoch;
+        return 0;
+    }
+    DeviceGuard g(h->device);
+    return install_image_from_host(h, (const uint8_t*)buf, len);
+}
+
+int sfc_table_export_device(const sfc_handle* hc, void* dptr, size_t len, void* cuda_stream) {
+    sfc_handle* h = const_cast<sfc_handle*>(hc);
+    if (!h || !dptr) return -EINVAL;
+    if (h->offline()) return fail(h, -ENODEV, "offline handle: no device (there is no CPU data path)");
+    if (!h->d_image) return fail(h, -ENOENT, "sfc_table_export_device: nothing committed");
+    if (len < h->image_bytes) return fail(h, -ENOSPC, "sfc_table_export_device: buffer too small");
+    DeviceGuard g(h->device);
+    CUDA_TRY(h, cudaMemcpyAsync(dptr, h->d_image, h->image_bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)cuda_stream));
+    return 0;
+}
+
+int sfc_table_import_device(sfc_handle* h, const void* dptr, size_t len, void* cuda_stream) {
+    if (!h || !dptr || len < kImageHeaderBytes) return -EINVAL;
+    if (h->offline()) return fail(h, -ENODEV, "offline handle: no device (there is no CPU data path)");
+    DeviceGuard g(h->device);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    // validate the header on the host before adopting the buffer
+    std::vector<uint8_t> head(kImageHeaderBytes);
+    CUDA_TRY(h, cudaMemcpyAsync(head.data(), dptr, kImageHeaderBytes, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(h, cudaStreamSynchronize(st));
+    ImageHeader H;
+    memcpy(&H, head.data(), sizeof(H));
+    if (H.magic != kImageMagic || H.version != kImageVersion || H.total_bytes != len)
+        return fail(h, -EINVAL, "sfc_table_import_device: bad magic, version or length");
+    uint8_t* d = nullptr;
+    CUDA_TRY(h, cudaMalloc(&d, len));
+    cudaError_t e = cudaMemcpyAsync(d, dptr, len, cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        cudaFree(d);
+        return fail(h, -EIO, "sfc_table_import_device: %s", cudaGetErrorString(e));
+    }
+    if (h->d_image) cudaFree(h->d_image);
+    h->d_image = d;
+    h->image_bytes = len;
+    bind_tables(h);
+    return 0;
+}
+
+// =================================================================== data plane ==========
+int sfc_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n, uint32_t flags,
+                 void* cuda_stream) {
+    if (!h) return -EINVAL;
+    if (h->offline()) return fail(h, -ENODEV, "offline handle: no device (there is no CPU data path)");
+    if (n == 0) return 0;
+    if (!hdr || !in_port || !result) return fail(h, -EINVAL, "sfc_classify: null buffer");
+    DeviceGuard g(h->device);
+    return launch_classify(h, hdr, in_port, result, n, flags, (cudaStream_t)cuda_stream);
+}
+
+int sfc_classify_host(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
+                      uint32_t flags) {
+    if (!h) return -EINVAL;
+    if (h->offline()) return fail(h, -ENODEV, "offline handle: no device (there is no CPU data path)");
+    if (n == 0) return 0;
+    if (!hdr || !in_port || !result) return fail(h, -EINVAL, "sfc_classify_host: null buffer");
+    DeviceGuard g(h->device);
+    if (!h->hs[0]) {
+        for (int i = 0; i < 2; ++i) {
+            CUDA_TRY(h, cudaStreamCreateWithFlags(&h->hs[i], cudaStreamNonBlocking));
+            CUDA_TRY(h, cudaEventCreate(&h->ev[i][0]));
+            CUDA_TRY(h, cudaEventCreate(&h->ev[i][1]));
+            CUDA_TRY(h, cudaMalloc(&h->d_hdr[i], kHostChunk * 64));
+            CUDA_TRY(h, cudaMalloc(&h->d_port[i], kHostChunk * 2));
+            CUDA_TRY(h, cudaMalloc(&h->d_res[i], kHostChunk * 8));
+        }
+    }
+    const uint8_t* hp = (const uint8_t*)hdr;
+    size_t n_chunks = (n + kHostChunk - 1) / kHostChunk;
+    float ms_total = 0.f;
+    for (size_t c = 0; c < n_chunks; ++c) {
+        int b = (int)(c & 1);
+        size_t off = c * kHostChunk, m = std::min(kHostChunk, n - off);
+        if (c >= 2) {  // buffer b was used by chunk c-2: wait for its D2H, collect its kernel time
+            CUDA_TRY(h, cudaStreamSynchronize(h->hs[b]));
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, h->ev[b][0], h->ev[b][1]);
+            ms_total += ms;
+        }
+        cudaStream_t st = h->hs[b];
+        CUDA_TRY(h, cudaMemcpyAsync(h->d_hdr[b], hp + off * 64, m * 64, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(h, cudaMemcpyAsync(h->d_port[b], in_port + off, m * 2, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(h, cudaEventRecord(h->ev[b][0], st));
+        int rc = launch_classify(h, h->d_hdr[b], h->d_port[b], h->d_res[b], m, flags, st);
+        if (rc) return rc;
+        CUDA_TRY(h, cudaEventRecord(h->ev[b][1], st));
+        CUDA_TRY(h, cudaMemcpyAsync(result + off, h->d_res[b], m * 8, cudaMemcpyDeviceToHost, st));
+    }
+    for (size_t c = (n_chunks >= 2 ? n_chunks - 2 : 0); c < n_chunks; ++c) {
+        int b = (int)(c & 1);
+        CUDA_TRY(h, cudaStreamSynchronize(h->hs[b]));
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[b][0], h->ev[b][1]);
+        ms_total += ms;
+    }
+    h->last_kernel_ms = ms_total;
+    return 0;
+}
+
+int sfc_sync(sfc_handle* h, void* cuda_stream) {
+    if (!h) return -EINVAL;
+    if (h->offline()) return fail(h, -ENODEV, "offline handle: no device");
+    DeviceGuard g(h->device);
+    CUDA_TRY(h, cudaStreamSynchronize((cudaStream_t)cuda_stream));
+    return 0;
+}
+
+int sfc_counters_read(sfc_handle* h, uint64_t* out, size_t n) {
+    if (!h || !out || n > SFC_CNT_TOTAL) return -EINVAL;
+    if (h->offline()) return fail(h, -ENODEV, "offline handle: no device");
+    DeviceGuard g(h->device);
+    CUDA_TRY(h, cudaDeviceSynchronize());
+    CUDA_TRY(h, cudaMemcpy(out, h->d_counters, n * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int sfc_counters_reset(sfc_handle* h) {
+    if (!h) return -EINVAL;
+    if (h->offline()) return fail(h, -ENODEV, "offline handle: no device");
+    DeviceGuard g(h->device);
+    CUDA_TRY(h, cudaDeviceSynchronize());
+    CUDA_TRY(h, cudaMemset(h->d_counters, 0, SFC_CNT_TOTAL * sizeof(uint64_t)));
+    return 0;
+}
+
+void* sfc_counters_device_ptr(sfc_handle* h) { return h ? (void*)h->d_counters : nullptr; }
+uint64_t sfc_launch_count(const sfc_handle* h) { return h ? h->launches : 0; }
+float sfc_last_kernel_ms(const sfc_handle* h) { return h ? h->last_kernel_ms : -1.f; }
+
+// =================================================================== generator ===========
+int sfc_gen_packets(sfc_handle* h, const sfc_gen_spec* spec, uint64_t first, size_t n, void* hdr_dev,
+                    uint16_t* in_port_dev, void* cuda_stream) {
+    if (!h || !spec) return -EINVAL;
+    if (h->offline()) return fail(h, -ENODEV, "offline handle: no device");
+    if (n == 0) return 0;
+    if (!hdr_dev || !in_port_dev) return fail(h, -EINVAL, "sfc_gen_packets: null buffer");
+    DeviceGuard g(h->device);
+    unsigned blocks = (unsigned)((n + 255) / 256);
+    gen_kernel<<<blocks, 256, 0, (cudaStream_t)cuda_stream>>>(*spec, first, (uint64_t)n, (uint8_t*)hdr_dev, in_port_dev);
+    CUDA_TRY(h, cudaGetLastError());
+    ++h->launches;
+    return 0;
+}
+
+void sfc_gen_packets_host(const sfc_gen_spec* spec, uint64_t first, size_t n, uint8_t* hdr, uint16_t* in_port) {
+    for (size_t i = 0; i < n; ++i) gen_packet(*spec, first + i, hdr + i * 64, in_port[i]);
+}
+
+void sfc_gen_flows(const sfc_gen_spec* spec, uint32_t first, size_t n, sfc_flow_key* keys, sfc_flow_action* acts) {
+    for (size_t i = 0; i < n; ++i) {
+        GenFlow f;
+        gen_flow(*spec, first + (uint32_t)i, f);
+        sfc_flow_key& k = keys[i];
+        memset(&k, 0, sizeof(k));
+        for (int w = 0; w < (f.ip_ver == 6 ? 4 : 1); ++w) {
+            put32(k.src + 4 * w, f.sip[w]);
+            put32(k.dst + 4 * w, f.dip[w]);
+        }
+        k.sport = (uint16_t)f.sport;
+        k.dport = (uint16_t)f.dport;
+        k.vlan = (uint16_t)f.vlan;
+        k.proto = (uint8_t)f.proto;
+        k.ip_ver = (uint8_t)f.ip_ver;
+        acts[i].action = (uint8_t)f.action;
+        acts[i].reserved = 0;
+        acts[i].out_port = (uint16_t)f.out_port;
+    }
+}
+
+void sfc_gen_mac(uint32_t i, uint8_t mac[6]) { gen_mac(i, mac); }
+
+void sfc_gen_prefix(const sfc_gen_spec* spec, int af, uint32_t j, uint8_t* prefix, int* len, uint16_t* out_port) {
+    uint32_t w[4], port;
+    int l;
+    gen_prefix(*spec, af, j, w, l, port);
+    for (int k = 0; k < (af == 6 ? 4 : 1); ++k) put32(prefix + 4 * k, w[k]);
+    if (len) *len = l;
+    if (out_port) *out_port = (uint16_t)port;
+}
+
+void sfc_gen_acl_rule(const sfc_gen_spec* spec, uint32_t j, sfc_acl_rule* r) {
+    memset(r, 0, sizeof(*r));
+    uint64_t a0 = draw(spec->seed_acl, 4ull * j), a1 = draw(spec->seed_acl, 4ull * j + 1);
+    uint64_t a2 = draw(spec->seed_acl, 4ull * j + 2), a3 = draw(spec->seed_acl, 4ull * j + 3);
+    bool v6 = spec->n_pfx6 && ((uint32_t)a0 % 10u) < 2u;
+    r->ip_ver = v6 ? 6 : 4;
+    // destination: a prefix of the LPM set, truncated to a coarse length, so traffic aimed at the
+    // prefix set meets the rule
+    uint32_t npfx = v6 ? spec->n_pfx6 : spec->n_pfx4;
+    uint32_t w[4] = {(uint32_t)(a1 >> 32), (uint32_t)a1, (uint32_t)(a2 >> 32), (uint32_t)a2}, port;
+    int plen = v6 ? 64 : 32;
+    if (npfx) gen_prefix(*spec, v6 ? 6 : 4, (uint32_t)(a1 >> 32) % npfx, w, plen, port);
+    const int cut4[4] = {8, 16, 24, 32}, cut6[4] = {32, 40, 48, 64};
+    int dlen = std::min(plen, (v6 ? cut6 : cut4)[(a0 >> 8) & 3]);
+    if (((a0 >> 12) & 7) == 0) dlen = 0;  // 1 in 8: any destination
+    for (int k = 0; k < (v6 ? 4 : 1); ++k) {
+        uint32_t m = mask32(dlen - 32 * k);
+        put32(r->dst + 4 * k, w[k] & m);
+        put32(r->dst_mask + 4 * k, m);
+    }
+    // source: mostly any, sometimes a short prefix
+    uint32_t sl = (uint32_t)(a0 >> 16) & 15u;
+    int slen = sl < 11 ? 0 : (sl < 14 ? 4 : 8);
+    put32(r->src, (uint32_t)(a2 >> 32) & mask32(slen));
+    put32(r->src_mask, mask32(slen));
+    if ((a0 >> 20) & 1) {
+        r->proto = ((a0 >> 21) & 1) ? 17 : 6;
+        r->proto_mask = 0xFF;
+    }
+    uint32_t dp = (uint32_t)(a0 >> 24) & 15u;
+    if (dp < 5) {  // exact destination port in a small well-known range
+        r->dport = (uint16_t)((a3 >> 8) & 0x3FF);
+        r->dport_mask = 0xFFFF;
+    } else if (dp < 8) {  // a block of 4096 ports
+        r->dport = (uint16_t)((a3 >> 8) & 0xF000);
+        r->dport_mask = 0xF000;
+    }
+    if (((a0 >> 28) & 15u) == 0) {
+        r->in_port = (uint16_t)(spec->port_base + ((uint32_t)(a3 >> 24) & 0xFFFF) % (spec->n_ports ? spec->n_ports : 1));
+        r->in_port_mask = 0xFFFF;
+    }
+    r->verdict = ((uint32_t)a3 % 10u) == 0 ? SFC_ACL_DENY : SFC_ACL_PERMIT;
+    // more specific rules outrank broader ones, with ties on purpose
+    uint32_t spec_bits = (uint32_t)dlen + (r->dport_mask == 0xFFFF ? 16u : (r->dport_mask ? 4u : 0u)) + (uint32_t)slen;
+    r->priority = 1u + spec_bits * 4u + (uint32_t)(a3 >> 32) % 4u;
+}
+
+}  // extern "C"

@@ -1,0 +1,437 @@
+// classify.cuh — the per-packet match-action pipeline as one persistent sm_100a kernel.
+//
+// Data movement: header records stream HBM -> shared memory through TMA (cp.async.bulk.tensor,
+// 64-byte swizzle so that "thread p reads packet p" is bank-conflict free), a ring of STAGES
+// tiles per CTA guarded by full/empty mbarriers, one producer lane and TILE consumer threads.
+// Each consumer owns one packet of a tile: 4 x LDS.128 -> registers, slot released at once,
+// then parse -> ACL -> flow probe -> L2 steering -> LPM, and one 8-byte result store.
+// Tables are read through the read-only global path (one 32-byte sector per flow-table probe).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/b200sfc.h"
+#include "sfc_common.h"
+
+namespace sfc {
+
+struct DevTables {
+    const uint32_t* flow4;
+    const uint32_t* flow6;
+    uint64_t flow4_seed, flow6_seed;
+    uint32_t flow4_nbuckets, flow4_nhash, flow4_count;
+    uint32_t flow6_nbuckets, flow6_nhash, flow6_count;
+    const L2Entry* l2x;
+    uint32_t l2x_mask, l2x_count;
+    const L2Wild* l2w;
+    uint32_t l2w_n, l2w_count;
+    const uint8_t* nf;
+    uint32_t nf_n;
+    const uint32_t* lpm4_root;
+    const uint32_t* lpm4_nodes;
+    const uint16_t* lpm4_nh;
+    uint32_t lpm4_count;
+    const uint32_t* lpm6_root;
+    const uint32_t* lpm6_nodes;
+    const uint16_t* lpm6_nh;
+    uint32_t lpm6_count;
+    const uint32_t* acl_bv;
+    const uint32_t* acl_base;  // [2][nwords]
+    const uint32_t* acl_rule;
+    uint32_t acl_nrules, acl_nwords, acl_npos4, acl_npos6;
+    uint8_t acl_pos4[kAclMaxPos], acl_pos6[kAclMaxPos], acl_slot4[kAclMaxPos], acl_slot6[kAclMaxPos];
+    unsigned long long* counters;
+};
+
+// ------------------------------------------------------------------ PTX helpers ----------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar,
+                                              uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+        " [%0], [%1, {%2, %3}], [%4], %5;" ::"r"(smem_u32(dst)),
+        "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)), "l"(policy)
+        : "memory");
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+// one 32-byte sector, read-only path
+__device__ __forceinline__ void ldg256(const void* p, uint32_t* r) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "l"(p));
+}
+__device__ __forceinline__ void stg_result(uint64_t* p, uint64_t v) {
+    asm volatile("st.global.cs.b64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t be32_pair(uint32_t lo_word, uint32_t hi_word) {
+    // big-endian value of the 4 bytes that start at byte 2 of lo_word
+    return __byte_perm(lo_word, hi_word, 0x2345);
+}
+__device__ __forceinline__ uint32_t word_at(const uint32_t* w, int i) {  // dynamic pick, i in 8..15
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 8; k < 16; ++k) v = (i == k) ? w[k] : v;
+    return v;
+}
+
+// ------------------------------------------------------------------ stage 0: parse -------
+// w[16]: the record as little-endian words.  Fills k; returns false for non-IP frames.
+__device__ __forceinline__ bool parse_header(uint32_t* w, Key& k) {
+    k.mac_hi = __byte_perm(w[0], 0, 0x4401);  // bytes 0,1 big-endian
+    k.mac_lo = be32_pair(w[0], w[1]);
+    uint32_t et = __byte_perm(w[3], 0, 0x4401);
+    uint32_t vlan = 0;
+    int limit = 64;
+    if (et == 0x8100u) {
+        vlan = __byte_perm(w[3], 0, 0x4423) & 0xFFFu;  // TCI = bytes 14,15
+        // a tag is exactly one word: slide the rest of the frame down by one
+#pragma unroll
+        for (int i = 3; i < 15; ++i) w[i] = w[i + 1];
+        w[15] = 0;
+        et = __byte_perm(w[3], 0, 0x4401);
+        limit = 60;
+    }
+    k.meta = vlan << 8;
+    k.ip_ver = 0;
+    k.ports = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) k.sip[i] = k.dip[i] = 0;
+    uint32_t vihl = (w[3] >> 16) & 0xFFu;  // byte 14
+    if (et == 0x0800u) {
+        uint32_t ihl = vihl & 0xFu;
+        if ((vihl >> 4) != 4u || ihl < 5u) return false;
+        uint32_t proto = w[5] >> 24;                          // byte 23
+        uint32_t frag = __byte_perm(w[5], 0, 0x4401) & 0x1FFFu;  // bytes 20,21
+        k.sip[0] = be32_pair(w[6], w[7]);
+        k.dip[0] = be32_pair(w[7], w[8]);
+        k.meta |= proto;
+        k.ip_ver = 4;
+        int l4 = 14 + 4 * (int)ihl;
+        bool has_ports = (proto == 6u || proto == 17u || proto == 132u) && frag == 0u && l4 + 4 <= limit;
+        if (has_ports) {
+            if (ihl == 5u)
+                k.ports = be32_pair(w[8], w[9]);
+            else  // options: L4 starts (ihl-5) words later
+                k.ports = be32_pair(word_at(w, 3 + (int)ihl), word_at(w, 4 + (int)ihl));
+        }
+        return true;
+    }
+    if (et == 0x86DDu) {
+        if ((vihl >> 4) != 6u) return false;
+        uint32_t proto = w[5] & 0xFFu;  // byte 20
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            k.sip[i] = be32_pair(w[5 + i], w[6 + i]);
+            k.dip[i] = be32_pair(w[9 + i], w[10 + i]);
+        }
+        k.meta |= proto;
+        k.ip_ver = 6;
+        if (proto == 6u || proto == 17u || proto == 132u) k.ports = be32_pair(w[13], w[14]);
+        return true;
+    }
+    return false;
+}
+
+// ------------------------------------------------------------------ stage 2: flows -------
+__device__ __forceinline__ bool flow4_lookup(const DevTables& T, const Key& k, uint32_t& m0, uint32_t& m1) {
+    uint32_t meta20 = k.meta & 0xFFFFFu;
+    uint64_t d = flow4_digest(k.sip[0], k.dip[0], k.ports, meta20, T.flow4_seed);
+    for (uint32_t j = 0; j < T.flow4_nhash; ++j) {
+        uint32_t b = flow_bucket(d, (int)j, T.flow4_nbuckets);
+        uint32_t s[8];
+        ldg256(T.flow4 + (size_t)b * (kFlow4BucketBytes / 4), s);
+        if (s[0] == k.sip[0] && s[1] == k.dip[0] && s[2] == k.ports && (s[3] & 0xFFFFFu) == meta20 &&
+            slot_action(s[3]) != 3u) {
+            m0 = s[3];
+            m1 = s[4];
+            return true;
+        }
+    }
+    return false;
+}
+__device__ __forceinline__ bool flow6_lookup(const DevTables& T, const Key& k, uint32_t& m0, uint32_t& m1) {
+    uint32_t meta20 = k.meta & 0xFFFFFu;
+    uint64_t d = flow6_digest(k.sip, k.dip, k.ports, meta20, T.flow6_seed);
+    for (uint32_t j = 0; j < T.flow6_nhash; ++j) {
+        uint32_t b = flow_bucket(d, (int)j, T.flow6_nbuckets);
+        const uint32_t* p = T.flow6 + (size_t)b * (kFlow6BucketBytes / 4);
+        uint32_t s[16];
+        ldg256(p, s);
+        ldg256(p + 8, s + 8);
+        bool eq = (s[8] == k.ports) && ((s[9] & 0xFFFFFu) == meta20) && slot_action(s[9]) != 3u;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) eq = eq && s[i] == k.sip[i] && s[4 + i] == k.dip[i];
+        if (eq) {
+            m0 = s[9];
+            m1 = s[10];
+            return true;
+        }
+    }
+    return false;
+}
+
+// ------------------------------------------------------------------ stage 4: LPM ---------
+template <int MAX_BITS>
+__device__ __forceinline__ uint32_t lpm_lookup(const uint32_t* __restrict__ root, const uint32_t* __restrict__ nodes,
+                                               const uint32_t* a) {
+    uint32_t e = __ldg(root + (a[0] >> 16));
+#pragma unroll
+    for (int pos = 16; pos < MAX_BITS; pos += 8) {  // static positions: the address stays in registers
+        if (!(e & kLpmChild)) break;
+        uint32_t byte = (a[pos >> 5] >> (24 - (pos & 31))) & 0xFFu;
+        e = __ldg(nodes + (size_t)(e & ~kLpmChild) * 256 + byte);
+    }
+    return (e & kLpmChild) ? 0u : e;
+}
+
+__device__ __forceinline__ uint32_t nf_of(const DevTables& T, uint32_t port) {
+    return port < T.nf_n ? (uint32_t)__ldg(T.nf + port) : (uint32_t)SFC_NF_NONE;
+}
+
+// ------------------------------------------------------------------ the kernel -----------
+template <int TILE, int STAGES>
+struct SmemLayout {
+    static constexpr int kTileBytes = TILE * 64;
+    static constexpr int kAclBytes = (TILE / 32) * kAclKeyWords * 32 * 4;
+    static constexpr int kBytes = STAGES * kTileBytes + kAclBytes + 2 * STAGES * 8 + 16 * 8 + 1024;
+};
+
+template <int TILE, int STAGES, bool COUNTERS, bool ACL>
+__global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
+                                                              const uint16_t* __restrict__ in_port,
+                                                              uint64_t* __restrict__ result, uint64_t n,
+                                                              uint32_t n_tiles,
+                                                              const __grid_constant__ DevTables T) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* tiles = smem;
+    uint32_t* aclq = (uint32_t*)(smem + STAGES * TILE * 64);
+    uint64_t* full = (uint64_t*)((uint8_t*)aclq + SmemLayout<TILE, STAGES>::kAclBytes);
+    uint64_t* empty = full + STAGES;
+    unsigned long long* scnt = (unsigned long long*)(empty + STAGES);  // 16 block-level counters
+
+    const int tid = threadIdx.x;
+    constexpr int kConsumerWarps = TILE / 32;
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(full + s, 1);
+            mbar_init(empty + s, kConsumerWarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (COUNTERS && tid < 16) scnt[tid] = 0;
+    __syncthreads();
+
+    if (tid >= TILE) {
+        // ---------------- producer warp: one lane feeds the ring ----------------
+        if (tid == TILE) {
+            uint64_t pol = policy_evict_first();
+            uint32_t it = 0;
+            for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+                uint32_t s = it % STAGES, use = it / STAGES;
+                if (use > 0) mbar_wait(empty + s, (use - 1) & 1);
+                mbar_arrive_expect_tx(full + s, TILE * 64);
+                tma_load_tile(tiles + s * TILE * 64, &hdr_map, 0, (int)(tile * TILE), full + s, pol);
+            }
+        }
+    } else {
+        // ---------------- consumers: one packet per thread per tile ----------------
+        const int lane = tid & 31, warp = tid >> 5;
+        const uint32_t row_off = (uint32_t)tid * 64u;
+        const uint32_t sw = ((uint32_t)tid >> 1) & 3u;
+        uint32_t it = 0;
+        for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+            uint32_t s = it % STAGES, use = it / STAGES;
+            uint64_t pkt = (uint64_t)tile * TILE + tid;
+            bool live = pkt < n;
+            uint32_t port = live ? (uint32_t)__ldg(in_port + pkt) : 0u;
+
+            mbar_wait(full + s, use & 1);
+            uint32_t w[16];
+            uint32_t base = smem_u32(tiles + s * TILE * 64) + row_off;
+#pragma unroll
+            for (uint32_t c = 0; c < 4; ++c) {
+                uint4 v = lds128(base + ((c ^ sw) << 4));
+                w[4 * c + 0] = v.x;
+                w[4 * c + 1] = v.y;
+                w[4 * c + 2] = v.z;
+                w[4 * c + 3] = v.w;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty + s);
+
+            Key k;
+            bool is_ip = parse_header(w, k);
+            uint64_t res = SFC_RESULT_MISS;
+            bool done = !live;  // lanes past the end of the batch hold zero-filled records
+
+            // ---- stage 1: ACL (warp-cooperative byte-sliced bit vectors) ----
+            if (ACL) {
+                uint32_t* q = aclq + warp * (kAclKeyWords * 32);
+                q[0 * 32 + lane] = (port << 16) | (k.meta >> 8);
+                q[1 * 32 + lane] = (k.ip_ver << 24) | ((k.meta & 0xFFu) << 16) | (k.ports >> 16);
+                q[2 * 32 + lane] = k.ports << 16;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    q[(3 + i) * 32 + lane] = k.sip[i];
+                    q[(7 + i) * 32 + lane] = k.dip[i];
+                }
+                __syncwarp();
+                uint32_t todo = __ballot_sync(0xFFFFFFFFu, live && is_ip);
+                uint32_t my_hit = 0xFFFFFFFFu;
+                while (todo) {
+                    int j = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    bool v6 = (q[1 * 32 + j] >> 24) == 6u;
+                    const uint8_t* pos = v6 ? T.acl_pos6 : T.acl_pos4;
+                    const uint8_t* slot = v6 ? T.acl_slot6 : T.acl_slot4;
+                    uint32_t npos = v6 ? T.acl_npos6 : T.acl_npos4;
+                    uint32_t best = 0xFFFFFFFFu;
+                    for (uint32_t wbase = 0; wbase < T.acl_nwords && best == 0xFFFFFFFFu; wbase += 32) {
+                        uint32_t wi = wbase + lane;
+                        bool in = wi < T.acl_nwords;
+                        uint32_t acc = in ? __ldg(T.acl_base + (v6 ? T.acl_nwords : 0) + wi) : 0u;
+                        for (uint32_t p = 0; p < npos; ++p) {
+                            uint32_t kb = pos[p];
+                            uint32_t val = (q[(kb >> 2) * 32 + j] >> (24 - 8 * (kb & 3))) & 0xFFu;
+                            if (in) acc &= __ldg(T.acl_bv + ((size_t)slot[p] * 256 + val) * T.acl_nwords + wi);
+                            if ((p & 3) == 3 && __ballot_sync(0xFFFFFFFFu, acc != 0) == 0) break;
+                        }
+                        uint32_t any = __ballot_sync(0xFFFFFFFFu, acc != 0);
+                        if (any) {
+                            int src = __ffs(any) - 1;
+                            uint32_t word = __shfl_sync(0xFFFFFFFFu, acc, src);
+                            best = (wbase + src) * 32 + (__ffs(word) - 1);
+                        }
+                    }
+                    if (lane == j) my_hit = best;
+                }
+                __syncwarp();
+                if (my_hit != 0xFFFFFFFFu) {
+                    uint32_t r = __ldg(T.acl_rule + my_hit);
+                    if (COUNTERS) atomicAdd(T.counters + SFC_CNT_RULES0 + (r & 0x0FFFFFFFu), 1ull);
+                    if (r & 0x80000000u) {
+                        res = SFC_RESULT(SFC_ACT_DROP, SFC_NF_NONE, 0, SFC_STAGE_ACL, r & 0x0FFFFFFFu);
+                        done = true;
+                    }
+                }
+            }
+
+            // ---- stage 2: exact 5-tuple ----
+            if (!done && is_ip) {
+                uint32_t m0 = 0, m1 = 0;
+                bool hit = false;
+                if (k.ip_ver == 4) {
+                    if (T.flow4_count) hit = flow4_lookup(T, k, m0, m1);
+                } else if (T.flow6_count) {
+                    hit = flow6_lookup(T, k, m0, m1);
+                }
+                if (hit) {
+                    uint32_t act = slot_action(m0), op = slot_port(m1);
+                    uint32_t nf = act == SFC_ACT_FORWARD ? nf_of(T, op) : (uint32_t)SFC_NF_NONE;
+                    res = SFC_RESULT(act, nf, op, SFC_STAGE_FLOW, slot_id(m0, m1));
+                    done = true;
+                }
+            }
+
+            // ---- stage 3: SFC L2 steering ----
+            if (!done) {
+                if (T.l2x_count) {
+                    uint32_t key_hi = (port << 16) | k.mac_hi;
+                    uint32_t i = l2_hash(key_hi, k.mac_lo) & T.l2x_mask;
+                    for (;;) {
+                        uint4 e = __ldg(reinterpret_cast<const uint4*>(T.l2x + i));
+                        if (!(e.w & 0x80000000u)) break;
+                        if (e.x == k.mac_lo && e.y == key_hi) {
+                            uint32_t op = e.w & 0xFFFFu;
+                            res = SFC_RESULT(SFC_ACT_FORWARD, nf_of(T, op), op, SFC_STAGE_L2_EXACT, e.z);
+                            done = true;
+                            if (COUNTERS) atomicAdd(T.counters + SFC_CNT_L2_0 + (e.z % SFC_CNT_L2_N), 1ull);
+                            break;
+                        }
+                        i = (i + 1) & T.l2x_mask;
+                    }
+                }
+                if (!done && T.l2w_count && port < T.l2w_n) {
+                    uint2 e = __ldg(reinterpret_cast<const uint2*>(T.l2w + port));
+                    if (e.x & 0x80000000u) {
+                        uint32_t op = e.x & 0xFFFFu;
+                        res = SFC_RESULT(SFC_ACT_FORWARD, nf_of(T, op), op, SFC_STAGE_L2_WILD, e.y);
+                        done = true;
+                        if (COUNTERS) atomicAdd(T.counters + SFC_CNT_L2_0 + (e.y % SFC_CNT_L2_N), 1ull);
+                    }
+                }
+            }
+
+            // ---- stage 4: LPM on the destination ----
+            if (!done && is_ip) {
+                if (k.ip_ver == 4 && T.lpm4_count) {
+                    uint32_t e = lpm_lookup<32>(T.lpm4_root, T.lpm4_nodes, k.dip);
+                    if (e) {
+                        uint32_t op = __ldg(T.lpm4_nh + (e - 1));
+                        res = SFC_RESULT(SFC_ACT_FORWARD, nf_of(T, op), op, SFC_STAGE_LPM4, e - 1);
+                    }
+                } else if (k.ip_ver == 6 && T.lpm6_count) {
+                    uint32_t e = lpm_lookup<128>(T.lpm6_root, T.lpm6_nodes, k.dip);
+                    if (e) {
+                        uint32_t op = __ldg(T.lpm6_nh + (e - 1));
+                        res = SFC_RESULT(SFC_ACT_FORWARD, nf_of(T, op), op, SFC_STAGE_LPM6, e - 1);
+                    }
+                }
+            }
+
+            if (live) stg_result(result + pkt, res);
+
+            if (COUNTERS) {
+                uint32_t act = SFC_RESULT_ACTION(res), stage = SFC_RESULT_STAGE(res);
+#pragma unroll
+                for (uint32_t a = 0; a < 3; ++a) {
+                    uint32_t m = __ballot_sync(0xFFFFFFFFu, live && act == a);
+                    if (lane == 0 && m) atomicAdd(scnt + SFC_CNT_ACTION0 + a, (unsigned long long)__popc(m));
+                }
+#pragma unroll
+                for (uint32_t st = 0; st < 7; ++st) {
+                    uint32_t m = __ballot_sync(0xFFFFFFFFu, live && stage == st);
+                    if (lane == 0 && m) atomicAdd(scnt + SFC_CNT_STAGE0 + st, (unsigned long long)__popc(m));
+                }
+            }
+        }
+    }
+    if (COUNTERS) {
+        __syncthreads();
+        if (tid < 16 && scnt[tid]) atomicAdd(T.counters + tid, scnt[tid]);
+    }
+}
+
+}  // namespace sfc

@@ -1,0 +1,556 @@
+// tables.cpp — host-side table-image builder.  See tables.h.
+#include "tables.h"
+
+#include <algorithm>
+#include <cstring>
+
+namespace sfc {
+
+// ------------------------------------------------------------------ FlowIndex ------------
+uint64_t FlowIndex::hash(const FlowRec& k) {
+    uint64_t h = 0x243F6A8885A308D3ull ^ k.ip_ver;
+    for (int i = 0; i < 4; ++i) h = mix64(h ^ (((uint64_t)k.sip[i] << 32) | k.dip[i]));
+    return mix64(h ^ (((uint64_t)k.ports << 32) | k.meta));
+}
+static bool same_key(const FlowRec& a, const FlowRec& b) {
+    return a.ip_ver == b.ip_ver && a.ports == b.ports && a.meta == b.meta &&
+           !memcmp(a.sip, b.sip, 16) && !memcmp(a.dip, b.dip, 16);
+}
+void FlowIndex::clear() {
+    slots_.clear();
+    used_ = 0;
+}
+int64_t FlowIndex::find(const std::vector<FlowRec>& recs, const FlowRec& k) const {
+    if (slots_.empty()) return -1;
+    size_t mask = slots_.size() - 1;
+    for (size_t i = hash(k) & mask;; i = (i + 1) & mask) {
+        uint32_t s = slots_[i];
+        if (!s) return -1;
+        if (same_key(recs[s - 1], k)) return (int64_t)s - 1;
+    }
+}
+void FlowIndex::grow(const std::vector<FlowRec>& recs, size_t want) {
+    size_t cap = 1024;
+    while (cap < want * 2) cap <<= 1;
+    slots_.assign(cap, 0);
+    used_ = 0;
+    for (uint32_t p = 0; p < recs.size(); ++p) {
+        size_t mask = cap - 1, i = hash(recs[p]) & mask;
+        while (slots_[i]) i = (i + 1) & mask;
+        slots_[i] = p + 1;
+        ++used_;
+    }
+}
+void FlowIndex::rebuild(const std::vector<FlowRec>& recs, size_t expect) {
+    grow(recs, std::max(expect, recs.size()));
+}
+void FlowIndex::insert(const std::vector<FlowRec>& recs, uint32_t pos) {
+    if (slots_.empty() || (used_ + 1) * 2 > slots_.size()) {
+        // recs already contains pos; grow() re-inserts everything including it
+        grow(recs, std::max<size_t>(recs.size() * 2, 512));
+        return;
+    }
+    size_t mask = slots_.size() - 1, i = hash(recs[pos]) & mask;
+    while (slots_[i]) i = (i + 1) & mask;
+    slots_[i] = pos + 1;
+    ++used_;
+}
+
+void RuleStore::clear_rules() {
+    l2.clear();
+    next_l2_id = 0;
+    nf_in.clear();
+    nf_out.clear();
+    flows.clear();
+    flow_index.clear();
+    next_flow_id = 0;
+    lpm4.clear();
+    lpm6.clear();
+    next_lpm_id = 0;
+    acl.clear();
+    next_acl_id = 0;
+}
+
+static uint32_t be32(const uint8_t* p) {
+    return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3];
+}
+
+bool flow_from_key(const sfc_flow_key& k, const sfc_flow_action& a, FlowRec& out, std::string& err) {
+    if (k.ip_ver != 4 && k.ip_ver != 6) {
+        err = "flow key: ip_ver must be 4 or 6";
+        return false;
+    }
+    if (k.vlan > 4095) {
+        err = "flow key: vlan must be 0..4095";
+        return false;
+    }
+    if (a.action > SFC_ACT_DROP) {
+        err = "flow action: unknown action";
+        return false;
+    }
+    if (a.action != SFC_ACT_FORWARD && a.out_port != 0) {
+        err = "flow action: out_port must be 0 unless action is FORWARD";
+        return false;
+    }
+    if (a.out_port >= SFC_MAX_PORTS) {
+        err = "flow action: out_port out of range";
+        return false;
+    }
+    if (k.ip_ver == 4)
+        for (int i = 4; i < 16; ++i)
+            if (k.src[i] || k.dst[i]) {
+                err = "flow key: IPv4 address bytes 4..15 must be zero";
+                return false;
+            }
+    for (int i = 0; i < 4; ++i) {
+        out.sip[i] = be32(k.src + 4 * i);
+        out.dip[i] = be32(k.dst + 4 * i);
+    }
+    out.ports = ((uint32_t)k.sport << 16) | k.dport;
+    out.meta = (uint32_t)k.proto | ((uint32_t)k.vlan << 8);
+    out.ip_ver = k.ip_ver;
+    out.action = a.action;
+    out.out_port = a.out_port;
+    out.id = 0;
+    return true;
+}
+
+// ------------------------------------------------------------------ image assembly -------
+namespace {
+
+struct Blob {
+    std::vector<uint8_t>& img;
+    explicit Blob(std::vector<uint8_t>& v) : img(v) {}
+    uint64_t reserve(size_t bytes, uint8_t fill) {
+        size_t off = (img.size() + kImageAlign - 1) / kImageAlign * kImageAlign;
+        img.resize(off, 0);
+        img.resize(off + bytes, fill);
+        return off;
+    }
+    template <class T>
+    T* at(uint64_t off) {
+        return reinterpret_cast<T*>(img.data() + off);
+    }
+};
+
+// ---- cuckoo ------------------------------------------------------------------------------
+template <int KEYW, int SLOTW, int BUCKET_BYTES, int SLOTS>
+struct Cuckoo {
+    static constexpr int BW = BUCKET_BYTES / 4;
+    uint32_t* tab;
+    uint32_t nbuckets;
+    int nhash;
+    uint64_t seed;
+    uint64_t rng = 0x1234567ull;
+
+    static uint64_t digest(const uint32_t* s, uint64_t seed) {
+        if (KEYW == kFlow4KeyWords) return flow4_digest(s[0], s[1], s[2], s[KEYW] & 0xFFFFFu, seed);
+        return flow6_digest(s, s + 4, s[8], s[KEYW] & 0xFFFFFu, seed);
+    }
+    uint32_t* slot(uint32_t b, int s) { return tab + (size_t)b * BW + s * SLOTW; }
+    static bool empty(const uint32_t* s) { return slot_action(s[KEYW]) == 3u; }
+
+    bool insert(const uint32_t* rec) {
+        uint32_t cur[SLOTW], tmp[SLOTW];
+        memcpy(cur, rec, sizeof(cur));
+        uint32_t came_from = 0xFFFFFFFFu;
+        for (int kick = 0; kick < 2000; ++kick) {
+            uint64_t d = digest(cur, seed);
+            uint32_t b[kMaxHashes];
+            for (int j = 0; j < nhash; ++j) {
+                b[j] = flow_bucket(d, j, nbuckets);
+                for (int s = 0; s < SLOTS; ++s) {
+                    uint32_t* p = slot(b[j], s);
+                    if (empty(p)) {
+                        memcpy(p, cur, 4 * SLOTW);
+                        return true;
+                    }
+                }
+            }
+            rng = mix64(rng + kGamma);
+            int j = (int)(rng % (uint64_t)nhash);
+            if (b[j] == came_from) j = (j + 1) % nhash;
+            int s = (int)((rng >> 32) % SLOTS);
+            uint32_t* p = slot(b[j], s);
+            memcpy(tmp, p, 4 * SLOTW);
+            memcpy(p, cur, 4 * SLOTW);
+            memcpy(cur, tmp, 4 * SLOTW);
+            came_from = b[j];
+        }
+        return false;
+    }
+};
+
+template <int KEYW, int SLOTW, int BUCKET_BYTES, int SLOTS>
+bool build_cuckoo(Blob& blob, const std::vector<const FlowRec*>& recs, int load_pct, int nhash,
+                  uint64_t& off, uint32_t& nbuckets, uint64_t& seed_out, std::string& err) {
+    size_t n = recs.size();
+    int max_load = (SLOTS == 1) ? (nhash == 2 ? 45 : 85) : 90;
+    load_pct = std::min(std::max(load_pct, 5), max_load);
+    uint64_t nb = std::max<uint64_t>(8, (n * 100 + (uint64_t)load_pct * SLOTS - 1) / ((uint64_t)load_pct * SLOTS));
+    for (int grow = 0; grow < 6; ++grow, nb = nb + nb / 8 + 1) {
+        if (nb > 0xFFFFFFF0ull) break;
+        for (int attempt = 0; attempt < 4; ++attempt) {
+            size_t start = blob.img.size();
+            off = blob.reserve((size_t)nb * BUCKET_BYTES, 0xFF);
+            Cuckoo<KEYW, SLOTW, BUCKET_BYTES, SLOTS> c;
+            c.tab = blob.at<uint32_t>(off);
+            c.nbuckets = (uint32_t)nb;
+            c.nhash = nhash;
+            c.seed = mix64(0x5FC0C0DEull + 977ull * attempt + 31ull * grow);
+            bool ok = true;
+            uint32_t rec[SLOTW];
+            for (size_t i = 0; i < n && ok; ++i) {
+                const FlowRec& f = *recs[i];
+                for (int w = 0; w < SLOTW; ++w) rec[w] = 0;
+                if (KEYW == kFlow4KeyWords) {
+                    rec[0] = f.sip[0];
+                    rec[1] = f.dip[0];
+                    rec[2] = f.ports;
+                } else {
+                    for (int w = 0; w < 4; ++w) {
+                        rec[w] = f.sip[w];
+                        rec[4 + w] = f.dip[w];
+                    }
+                    rec[8] = f.ports;
+                }
+                rec[KEYW] = slot_m0(f.meta, f.action, f.id);
+                rec[KEYW + 1] = slot_m1(f.out_port, f.id);
+                ok = c.insert(rec);
+            }
+            if (ok) {
+                nbuckets = (uint32_t)nb;
+                seed_out = c.seed;
+                return true;
+            }
+            blob.img.resize(start);
+        }
+    }
+    err = "flow table: cuckoo insertion did not converge";
+    return false;
+}
+
+// ---- LPM ---------------------------------------------------------------------------------
+inline uint32_t addr_bits(const uint32_t* w, int pos, int n) {  // n <= 16, MSB-first bit string
+    uint64_t two = ((uint64_t)w[pos >> 5] << 32) | ((pos >> 5) < 3 ? w[(pos >> 5) + 1] : 0u);
+    int sh = 64 - (pos & 31) - n;
+    return (uint32_t)(two >> sh) & ((1u << n) - 1u);
+}
+
+struct Trie {
+    std::vector<uint32_t> root = std::vector<uint32_t>(65536, 0);
+    std::vector<uint32_t> nodes;  // 256 entries per node
+
+    void fill(std::vector<uint32_t>& arr, size_t idx, uint32_t val) {
+        uint32_t e = arr[idx];
+        if (e & kLpmChild) {
+            size_t base = (size_t)(e & ~kLpmChild) * 256;
+            for (int i = 0; i < 256; ++i) fill(nodes, base + i, val);
+        } else {
+            arr[idx] = val;
+        }
+    }
+    // make sure arr[idx] is a child pointer; returns child number
+    uint32_t ensure_child(bool in_root, size_t idx) {
+        uint32_t e = in_root ? root[idx] : nodes[idx];
+        if (e & kLpmChild) return e & ~kLpmChild;
+        uint32_t child = (uint32_t)(nodes.size() / 256);
+        nodes.resize(nodes.size() + 256, e);  // leaf push: inherit the covering prefix
+        (in_root ? root[idx] : nodes[idx]) = kLpmChild | child;
+        return child;
+    }
+    void insert(const uint32_t* w, int len, uint32_t val) {
+        if (len <= 16) {
+            uint32_t first = len ? (addr_bits(w, 0, 16) & ~((1u << (16 - len)) - 1u)) : 0u;
+            uint32_t cnt = 1u << (16 - len);
+            for (uint32_t i = 0; i < cnt; ++i) fill(root, first + i, val);
+            return;
+        }
+        bool in_root = true;
+        size_t idx = addr_bits(w, 0, 16);
+        int consumed = 16;
+        while (len > consumed + 8) {
+            uint32_t child = ensure_child(in_root, idx);
+            idx = (size_t)child * 256 + addr_bits(w, consumed, 8);
+            in_root = false;
+            consumed += 8;
+        }
+        uint32_t child = ensure_child(in_root, idx);
+        int free_bits = consumed + 8 - len;
+        uint32_t first = addr_bits(w, consumed, 8) & ~((1u << free_bits) - 1u);
+        for (uint32_t i = 0; i < (1u << free_bits); ++i) fill(nodes, (size_t)child * 256 + first + i, val);
+    }
+};
+
+void build_lpm(Blob& blob, const std::map<RuleStore::LpmKey, LpmRec>& recs_map, uint64_t& root_off, uint64_t& nodes_off,
+               uint64_t& nh_off, uint32_t& nnodes, uint32_t& count) {
+    std::vector<const LpmRec*> sorted;
+    std::vector<LpmRec> recs;
+    recs.reserve(recs_map.size());
+    for (auto& kv : recs_map) recs.push_back(kv.second);
+    sorted.reserve(recs.size());
+    for (auto& r : recs) sorted.push_back(&r);
+    std::stable_sort(sorted.begin(), sorted.end(),
+                     [](const LpmRec* a, const LpmRec* b) { return a->len < b->len; });
+    Trie t;
+    uint32_t max_id = 0;
+    for (auto* r : sorted) {
+        t.insert(r->w, r->len, r->id + 1);
+        max_id = std::max(max_id, r->id);
+    }
+    count = (uint32_t)recs.size();
+    nnodes = (uint32_t)(t.nodes.size() / 256);
+    root_off = blob.reserve(65536 * 4, 0);
+    memcpy(blob.at<uint8_t>(root_off), t.root.data(), 65536 * 4);
+    nodes_off = blob.reserve(std::max<size_t>(t.nodes.size() * 4, 4), 0);
+    if (!t.nodes.empty()) memcpy(blob.at<uint8_t>(nodes_off), t.nodes.data(), t.nodes.size() * 4);
+    size_t nh_n = recs.empty() ? 1 : (size_t)max_id + 1;
+    nh_off = blob.reserve(nh_n * 2, 0);
+    for (auto& r : recs) blob.at<uint16_t>(nh_off)[r.id] = r.out_port;
+}
+
+// ---- ACL ---------------------------------------------------------------------------------
+void acl_key_bytes(const sfc_acl_rule& r, uint8_t* val, uint8_t* mask) {
+    memset(val, 0, kAclKeyBytes);
+    memset(mask, 0, kAclKeyBytes);
+    auto put16 = [&](int i, uint16_t v, uint16_t m) {
+        val[i] = v >> 8;
+        val[i + 1] = v & 0xFF;
+        mask[i] = m >> 8;
+        mask[i + 1] = m & 0xFF;
+    };
+    put16(0, r.in_port, r.in_port_mask);
+    put16(2, r.vlan, r.vlan_mask);
+    val[4] = r.ip_ver;
+    mask[4] = r.ip_ver ? 0xFF : 0;
+    val[5] = r.proto;
+    mask[5] = r.proto_mask;
+    put16(6, r.sport, r.sport_mask);
+    put16(8, r.dport, r.dport_mask);
+    for (int i = 0; i < 16; ++i) {
+        val[12 + i] = r.src[i];
+        mask[12 + i] = r.src_mask[i];
+        val[28 + i] = r.dst[i];
+        mask[28 + i] = r.dst_mask[i];
+    }
+}
+
+void build_acl(Blob& blob, const std::vector<AclRec>& recs, ImageHeader& H) {
+    std::vector<const AclRec*> sorted;
+    for (auto& r : recs) sorted.push_back(&r);
+    std::stable_sort(sorted.begin(), sorted.end(), [](const AclRec* a, const AclRec* b) {
+        if (a->r.priority != b->r.priority) return a->r.priority > b->r.priority;
+        return a->id < b->id;
+    });
+    uint32_t n = (uint32_t)sorted.size();
+    uint32_t nwords = (n + 31) / 32;
+    H.acl_nrules = n;
+    H.acl_nwords = nwords;
+    H.acl_npos4 = H.acl_npos6 = H.acl_nstored = 0;
+    if (!n) {
+        H.acl_bv_off = H.acl_base_off = H.acl_rule_off = blob.reserve(16, 0);
+        return;
+    }
+    std::vector<uint8_t> val((size_t)n * kAclKeyBytes), mask((size_t)n * kAclKeyBytes);
+    for (uint32_t i = 0; i < n; ++i)
+        acl_key_bytes(sorted[i]->r, &val[(size_t)i * kAclKeyBytes], &mask[(size_t)i * kAclKeyBytes]);
+    bool active[kAclKeyBytes];
+    for (int p = 0; p < kAclKeyBytes; ++p) {
+        active[p] = false;
+        for (uint32_t i = 0; i < n; ++i)
+            if (mask[(size_t)i * kAclKeyBytes + p]) active[p] = true;
+    }
+    auto bit = [&](uint32_t i, int p, uint32_t v) {
+        uint8_t m = mask[(size_t)i * kAclKeyBytes + p];
+        return ((v & m) == (val[(size_t)i * kAclKeyBytes + p] & m));
+    };
+    // bitmaps folded into the per-version base: positions whose packet byte is a constant
+    auto folded4 = [](int p) { return p == 4 || (p >= 16 && p < 28) || (p >= 32 && p < 44); };
+    auto folded6 = [](int p) { return p == 4; };
+    H.acl_base_off = blob.reserve((size_t)2 * nwords * 4, 0);
+    {
+        uint32_t* b4 = blob.at<uint32_t>(H.acl_base_off);
+        uint32_t* b6 = b4 + nwords;
+        for (uint32_t i = 0; i < n; ++i) {
+            bool m4 = true, m6 = true;
+            for (int p = 0; p < kAclKeyBytes; ++p) {
+                if (folded4(p) && !bit(i, p, p == 4 ? 4u : 0u)) m4 = false;
+                if (folded6(p) && !bit(i, p, 6u)) m6 = false;
+            }
+            if (m4) b4[i >> 5] |= 1u << (i & 31);
+            if (m6) b6[i >> 5] |= 1u << (i & 31);
+        }
+    }
+    // stored position tables
+    int slot_of[kAclKeyBytes];
+    uint32_t nstored = 0;
+    for (int p = 0; p < kAclKeyBytes; ++p) slot_of[p] = (active[p] && p != 4) ? (int)nstored++ : -1;
+    H.acl_nstored = nstored;
+    H.acl_bv_off = blob.reserve(std::max<size_t>((size_t)nstored * 256 * nwords * 4, 16), 0);
+    uint32_t* bv = blob.at<uint32_t>(H.acl_bv_off);
+    for (int p = 0; p < kAclKeyBytes; ++p) {
+        if (slot_of[p] < 0) continue;
+        for (uint32_t v = 0; v < 256; ++v) {
+            uint32_t* row = bv + ((size_t)slot_of[p] * 256 + v) * nwords;
+            for (uint32_t i = 0; i < n; ++i)
+                if (bit(i, p, v)) row[i >> 5] |= 1u << (i & 31);
+        }
+    }
+    // per-version position lists, most selective (fewest set bits on average) first
+    auto selectivity = [&](int p) {
+        uint64_t ones = 0;
+        const uint32_t* t = bv + (size_t)slot_of[p] * 256 * nwords;
+        for (size_t k = 0; k < (size_t)256 * nwords; ++k) ones += (uint64_t)__builtin_popcount(t[k]);
+        return ones;
+    };
+    std::vector<std::pair<uint64_t, int>> order;
+    for (int p = 0; p < kAclKeyBytes; ++p)
+        if (slot_of[p] >= 0) order.push_back({selectivity(p), p});
+    std::sort(order.begin(), order.end());
+    for (auto& o : order) {
+        int p = o.second;
+        if (!folded4(p)) {
+            H.acl_pos4[H.acl_npos4] = (uint8_t)p;
+            H.acl_slot4[H.acl_npos4++] = (uint8_t)slot_of[p];
+        }
+        if (!folded6(p)) {
+            H.acl_pos6[H.acl_npos6] = (uint8_t)p;
+            H.acl_slot6[H.acl_npos6++] = (uint8_t)slot_of[p];
+        }
+    }
+    H.acl_rule_off = blob.reserve((size_t)n * 4, 0);
+    uint32_t* ar = blob.at<uint32_t>(H.acl_rule_off);
+    for (uint32_t i = 0; i < n; ++i)
+        ar[i] = sorted[i]->id | (sorted[i]->r.verdict == SFC_ACL_DENY ? 0x80000000u : 0u);
+}
+
+}  // namespace
+
+bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& image, std::string& err) {
+    image.clear();
+    image.resize(kImageHeaderBytes, 0);
+    Blob blob(image);
+    ImageHeader H;
+    memset(&H, 0, sizeof(H));
+    H.magic = kImageMagic;
+    H.version = kImageVersion;
+    H.header_bytes = (uint32_t)kImageHeaderBytes;
+    H.epoch = epoch;
+
+    // flows, split by version
+    std::vector<const FlowRec*> f4, f6;
+    for (auto& f : rs.flows) (f.ip_ver == 4 ? f4 : f6).push_back(&f);
+    H.flow4_count = (uint32_t)f4.size();
+    H.flow6_count = (uint32_t)f6.size();
+    H.flow4_nhash = H.flow6_nhash = (uint32_t)rs.flow_hashes;
+    if (!build_cuckoo<kFlow4KeyWords, kFlow4SlotWords, kFlow4BucketBytes, kFlow4Slots>(
+            blob, f4, rs.flow_load_pct, rs.flow_hashes, H.flow4_off, H.flow4_nbuckets, H.flow4_seed, err))
+        return false;
+    if (!build_cuckoo<kFlow6KeyWords, kFlow6SlotWords, kFlow6BucketBytes, kFlow6Slots>(
+            blob, f6, rs.flow_load_pct, rs.flow_hashes, H.flow6_off, H.flow6_nbuckets, H.flow6_seed, err))
+        return false;
+
+    // L2 steering: resolve OpenFlow priorities per match, exact and wildcard apart
+    {
+        std::map<std::pair<uint32_t, uint32_t>, const L2Rule*> exact;  // (key_hi,key_lo) -> winner
+        std::map<uint16_t, const L2Rule*> wild;
+        auto better = [](const L2Rule* a, const L2Rule* b) {  // a beats b
+            return a->priority > b->priority || (a->priority == b->priority && a->id < b->id);
+        };
+        uint32_t max_port = 0;
+        for (auto& r : rs.l2) {
+            max_port = std::max<uint32_t>(max_port, r.in_port);
+            if (r.has_mac) {
+                uint32_t hi = ((uint32_t)r.in_port << 16) | ((uint32_t)r.mac[0] << 8) | r.mac[1];
+                uint32_t lo = be32(r.mac + 2);
+                auto key = std::make_pair(hi, lo);
+                auto it = exact.find(key);
+                if (it == exact.end() || better(&r, it->second)) exact[key] = &r;
+            } else {
+                auto it = wild.find(r.in_port);
+                if (it == wild.end() || better(&r, it->second)) wild[r.in_port] = &r;
+            }
+        }
+        uint32_t cap = 16;
+        while (cap < exact.size() * 2) cap <<= 1;
+        H.l2x_mask = cap - 1;
+        H.l2x_count = (uint32_t)exact.size();
+        H.l2x_off = blob.reserve((size_t)cap * sizeof(L2Entry), 0);
+        for (auto& kv : exact) {
+            L2Entry* tab = blob.at<L2Entry>(H.l2x_off);
+            uint32_t i = l2_hash(kv.first.first, kv.first.second) & H.l2x_mask;
+            while (tab[i].val & 0x80000000u) i = (i + 1) & H.l2x_mask;
+            tab[i].key_hi = kv.first.first;
+            tab[i].key_lo = kv.first.second;
+            tab[i].rule_id = kv.second->id;
+            tab[i].val = 0x80000000u | kv.second->out_port;
+        }
+        H.l2w_n = rs.l2.empty() ? 1 : max_port + 1;
+        H.l2w_count = (uint32_t)wild.size();
+        H.l2w_off = blob.reserve((size_t)H.l2w_n * sizeof(L2Wild), 0);
+        for (auto& kv : wild) {
+            L2Wild* w = blob.at<L2Wild>(H.l2w_off);
+            w[kv.first].val = 0x80000000u | kv.second->out_port;
+            w[kv.first].rule_id = kv.second->id;
+        }
+    }
+    // NF ownership of ports
+    {
+        uint32_t max_port = 0;
+        for (auto p : rs.nf_in) max_port = std::max<uint32_t>(max_port, p);
+        for (auto p : rs.nf_out) max_port = std::max<uint32_t>(max_port, p);
+        H.nf_n = max_port + 1;
+        H.nf_count = (uint32_t)rs.nf_in.size();
+        H.nf_off = blob.reserve(H.nf_n, (uint8_t)SFC_NF_NONE);
+        // first declaration wins if a port is named twice (lowest NF index)
+        for (size_t i = rs.nf_in.size(); i-- > 0;) {
+            blob.at<uint8_t>(H.nf_off)[rs.nf_out[i]] = (uint8_t)i;
+            blob.at<uint8_t>(H.nf_off)[rs.nf_in[i]] = (uint8_t)i;
+        }
+    }
+    build_lpm(blob, rs.lpm4, H.lpm4_root_off, H.lpm4_nodes_off, H.lpm4_nh_off, H.lpm4_nnodes, H.lpm4_count);
+    build_lpm(blob, rs.lpm6, H.lpm6_root_off, H.lpm6_nodes_off, H.lpm6_nh_off, H.lpm6_nnodes, H.lpm6_count);
+    build_acl(blob, rs.acl, H);
+
+    size_t total = (image.size() + kImageAlign - 1) / kImageAlign * kImageAlign;
+    image.resize(total, 0);
+    H.total_bytes = total;
+    memcpy(image.data(), &H, sizeof(H));
+    return true;
+}
+
+bool validate_image(const uint8_t* img, size_t len, std::string& err) {
+    if (len < kImageHeaderBytes) {
+        err = "image: shorter than its header";
+        return false;
+    }
+    ImageHeader H;
+    memcpy(&H, img, sizeof(H));
+    if (H.magic != kImageMagic || H.version != kImageVersion) {
+        err = "image: bad magic or version";
+        return false;
+    }
+    if (H.total_bytes != len || H.header_bytes != kImageHeaderBytes) {
+        err = "image: size field does not match the buffer length";
+        return false;
+    }
+    auto inside = [&](uint64_t off, uint64_t bytes) { return off >= kImageHeaderBytes && off + bytes <= len; };
+    bool ok = inside(H.flow4_off, (uint64_t)H.flow4_nbuckets * kFlow4BucketBytes) &&
+              inside(H.flow6_off, (uint64_t)H.flow6_nbuckets * kFlow6BucketBytes) &&
+              inside(H.l2x_off, ((uint64_t)H.l2x_mask + 1) * sizeof(L2Entry)) &&
+              ((H.l2x_mask & (H.l2x_mask + 1)) == 0) && inside(H.l2w_off, (uint64_t)H.l2w_n * sizeof(L2Wild)) &&
+              inside(H.nf_off, H.nf_n) && inside(H.lpm4_root_off, 65536 * 4) &&
+              inside(H.lpm4_nodes_off, (uint64_t)H.lpm4_nnodes * 1024) && inside(H.lpm6_root_off, 65536 * 4) &&
+              inside(H.lpm6_nodes_off, (uint64_t)H.lpm6_nnodes * 1024) && inside(H.lpm4_nh_off, 2) &&
+              inside(H.lpm6_nh_off, 2) && H.flow4_nhash >= 1 && H.flow4_nhash <= kMaxHashes &&
+              H.flow6_nhash >= 1 && H.flow6_nhash <= kMaxHashes && H.flow4_nbuckets && H.flow6_nbuckets &&
+              H.acl_npos4 <= kAclMaxPos && H.acl_npos6 <= kAclMaxPos && H.acl_nrules <= SFC_MAX_ACL_RULES;
+    if (ok && H.acl_nrules)
+        ok = inside(H.acl_bv_off, (uint64_t)H.acl_nstored * 256 * H.acl_nwords * 4) &&
+             inside(H.acl_base_off, (uint64_t)2 * H.acl_nwords * 4) &&
+             inside(H.acl_rule_off, (uint64_t)H.acl_nrules * 4);
+    if (!ok) err = "image: a section lies outside the buffer or a field is out of range";
+    return ok;
+}
+
+}  // namespace sfc

@@ -1,0 +1,100 @@
+// tables.h — host-side rule store and table-image builder (no CUDA in this file).
+//
+// The rule store mirrors what the reference's dataplane backends keep implicitly inside OVS:
+// ports by name (ovs-dp/ovsdp.go:40-62), steering flows by match (ovs-dp/ovsdp.go:113-162),
+// plus the synthesized tables of SURVEY.md §8a a12.  build_image() turns the staged rule set
+// into one contiguous, position-independent blob (ImageHeader + sections) that is uploaded to
+// HBM as is and can be broadcast rank to rank.
+#pragma once
+#include <array>
+#include <map>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/b200sfc.h"
+#include "sfc_common.h"
+
+namespace sfc {
+
+struct FlowRec {
+    uint32_t sip[4], dip[4];
+    uint32_t ports, meta;  // meta = proto | vlan << 8
+    uint32_t id;
+    uint8_t ip_ver, action;
+    uint16_t out_port;
+};
+
+struct L2Rule {
+    uint16_t in_port, out_port;
+    bool has_mac;
+    uint8_t mac[6];
+    uint32_t priority;  // OpenFlow priority: 10 / 100 / 32768 (ovs-dp/ovsdp.go:120,127,135)
+    uint32_t id;
+};
+
+struct LpmRec {
+    uint32_t w[4];
+    int len;
+    uint16_t out_port;
+    uint32_t id;
+};
+
+struct AclRec {
+    sfc_acl_rule r;
+    uint32_t id;
+};
+
+// open-addressing index over FlowRec (40-byte keys), for duplicate detection and delete
+class FlowIndex {
+  public:
+    void clear();
+    // returns position in recs or -1
+    int64_t find(const std::vector<FlowRec>& recs, const FlowRec& k) const;
+    void insert(const std::vector<FlowRec>& recs, uint32_t pos);
+    void rebuild(const std::vector<FlowRec>& recs, size_t expect);
+
+  private:
+    std::vector<uint32_t> slots_;  // pos+1, 0 = empty
+    size_t used_ = 0;
+    static uint64_t hash(const FlowRec& k);
+    void grow(const std::vector<FlowRec>& recs, size_t want);
+};
+
+struct RuleStore {
+    // ports
+    std::map<std::string, uint16_t> port_by_name;
+    std::vector<std::string> port_names;  // index = id, "" = free
+    // L2 steering
+    std::vector<L2Rule> l2;
+    uint32_t next_l2_id = 0;
+    // chain
+    std::vector<uint16_t> nf_in, nf_out;
+    // flows
+    std::vector<FlowRec> flows;
+    FlowIndex flow_index;
+    uint32_t next_flow_id = 0;
+    // LPM
+    typedef std::array<uint32_t, 5> LpmKey;  // len, w[0..3]
+    std::map<LpmKey, LpmRec> lpm4, lpm6;
+    uint32_t next_lpm_id = 0;
+    // ACL
+    std::vector<AclRec> acl;
+    uint32_t next_acl_id = 0;
+    // knobs
+    int flow_load_pct = 40;
+    int flow_hashes = 2;
+
+    void clear_rules();
+};
+
+// Converts a public flow key to the internal record; returns false if the key is malformed.
+bool flow_from_key(const sfc_flow_key& k, const sfc_flow_action& a, FlowRec& out, std::string& err);
+
+// Build the image.  Returns false and sets err on failure (e.g. cuckoo build could not converge).
+bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& image, std::string& err);
+
+// Structural validation of an image received from elsewhere (import / broadcast).
+bool validate_image(const uint8_t* img, size_t len, std::string& err);
+
+}  // namespace sfc

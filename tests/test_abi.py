@@ -1,0 +1,78 @@
+"""The C-ABI library loads on a CPU-only box and exports every symbol include/b200sfc.h declares."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from common import ROOT, sfc
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "b200sfc.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(sfc_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_declares_something():
+    syms = declared_symbols()
+    assert len(syms) >= 40 and "sfc_classify" in syms and "sfc_l2_rule_add" in syms
+
+
+def test_every_declared_symbol_is_exported():
+    L = ctypes.CDLL(sfc.LIB_PATH)
+    missing = [s for s in declared_symbols() if not hasattr(L, s)]
+    assert not missing, f"declared in b200sfc.h but not exported: {missing}"
+
+
+def test_python_bindings_cover_the_header():
+    bound = set(sfc.lib._sfc_signatures)
+    assert set(declared_symbols()) <= bound, set(declared_symbols()) - bound
+
+
+def test_no_cpu_fallback_without_a_gpu():
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(sfc.SfcError) as e:
+        sfc.Dataplane(0)
+    assert e.value.code == -19  # -ENODEV
+
+
+def test_offline_handle_refuses_data_plane_calls():
+    dp = sfc.Dataplane(-1)
+    dp.commit()
+    import numpy as np
+
+    with pytest.raises(sfc.SfcError) as e:
+        dp.classify_host(np.zeros((4, 64), np.uint8), np.zeros(4, np.uint16))
+    assert e.value.code == -19
+    with pytest.raises(sfc.SfcError):
+        dp.counters_read()
+
+
+def test_error_codes_and_messages():
+    dp = sfc.Dataplane(-1)
+    with pytest.raises(sfc.SfcError) as e:
+        dp.port_del("nope")
+    assert e.value.code == -2 and "nope" in str(e.value)
+    with pytest.raises(sfc.SfcError) as e:
+        dp.set_option("flow_load_pct", 1000)
+    assert e.value.code == -22
+    with pytest.raises(sfc.SfcError) as e:
+        dp.lpm_add(4, b"\x0a\x00\x00\x00", 33, 1)
+    assert e.value.code == -22
+
+
+def test_port_registry_semantics():
+    # ovs-vsctl --may-exist add-port / del-port / list-ports (ovs-dp/ovsdp.go:40-62,104-112)
+    dp = sfc.Dataplane(-1)
+    a, b = dp.port_add("eth0"), dp.port_add("vf0-1")
+    assert (a, b) == (0, 1)
+    assert dp.port_add("eth0") == 0  # --may-exist
+    assert dp.port_list() == ["eth0", "vf0-1"]
+    dp.port_del("eth0")
+    assert dp.port_list() == ["vf0-1"]
+    assert dp.port_add("nf-in") == 0  # lowest free id is reused
+    assert dp.port_lookup("vf0-1") == 1

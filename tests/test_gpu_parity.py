@@ -1,0 +1,257 @@
+"""GPU parity: the CUDA path, called through the C ABI, must be bit-exact against the CPU oracle
+on the same inputs (integer work: no tolerance)."""
+import numpy as np
+import pytest
+
+from common import Oracle, Scenario, config2_spec, config3_spec, config4_spec, consts, install_flows, install_lpm_acl, sfc
+from packets import handmade_cases
+
+pytestmark = pytest.mark.gpu
+
+
+def classify_dev(torch, dp, hdr_np, ports_np, flags=0):
+    hdr = torch.from_numpy(np.ascontiguousarray(hdr_np)).cuda()
+    ports = torch.from_numpy(ports_np.view(np.int16)).cuda()
+    res = torch.zeros(ports_np.size, dtype=torch.int64, device="cuda")
+    dp.classify(hdr.data_ptr(), ports.data_ptr(), res.data_ptr(), ports_np.size, flags, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    return res.cpu().numpy().view(np.uint64)
+
+
+def gen_dev(torch, dp, spec, first, n):
+    hdr = torch.empty((n, 64), dtype=torch.uint8, device="cuda")
+    ports = torch.empty(n, dtype=torch.int16, device="cuda")
+    dp.gen_packets(spec, first, n, hdr.data_ptr(), ports.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    return hdr, ports
+
+
+def assert_same(got, want, hdr=None):
+    bad = np.nonzero(got != want)[0]
+    if bad.size:
+        i = int(bad[0])
+        msg = f"{bad.size} of {got.size} results differ; first at packet {i}: got {int(got[i]):#018x} want {int(want[i]):#018x}"
+        if hdr is not None:
+            msg += f"\nheader: {bytes(np.asarray(hdr)[i]).hex()}"
+        raise AssertionError(msg)
+
+
+def test_generator_host_equals_device(torch_cuda):
+    dp = sfc.Dataplane(0)
+    spec = config3_spec(n_flows=5000, n_pfx4=100, n_pfx6=50, lpm_permille=500)
+    hdr_h, ports_h = sfc.gen_packets_host(spec, 12345, 20000)
+    hdr_d, ports_d = gen_dev(torch_cuda, dp, spec, 12345, 20000)
+    assert np.array_equal(hdr_d.cpu().numpy(), hdr_h)
+    assert np.array_equal(ports_d.cpu().numpy().view(np.uint16), ports_h)
+
+
+def test_handmade_edge_cases(torch_cuda):
+    """Tagged / double tagged / IPv4 options up to the 64-byte limit / fragments / IPv6 / malformed
+    version and IHL / non-IP, with rules in every table, against both oracles."""
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp, with_py=True)
+    hdr, ports = handmade_cases(sc)
+    dp.commit()
+    got = classify_dev(torch_cuda, dp, hdr, ports)
+    want = sc.orc.classify(hdr, ports)
+    assert_same(got, want, hdr)
+    want_py = np.array([sc.py.classify(bytes(hdr[i]), int(ports[i])) for i in range(len(ports))], dtype=np.uint64)
+    assert_same(got, want_py, hdr)
+    # every stage must have been exercised by the fixture
+    assert set(sfc.result_fields(got)[3].tolist()) == set(range(7))
+
+
+@pytest.mark.parametrize("n", [1, 31, 127, 128, 129, 4096, 100003])
+def test_ragged_sizes(torch_cuda, n):
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    spec = config2_spec()
+    install_flows(sc, spec)
+    sc.build_chain(8, 1)
+    dp.commit()
+    hdr, ports = sfc.gen_packets_host(spec, 7, n)
+    assert_same(classify_dev(torch_cuda, dp, hdr, ports), sc.orc.classify(hdr, ports), hdr)
+
+
+def test_empty_batch_and_empty_tables(torch_cuda):
+    dp = sfc.Dataplane(0)
+    dp.commit()
+    dp.classify(0, 0, 0, 0)  # n == 0: no launch, no error
+    hdr, ports = sfc.gen_packets_host(config2_spec(), 0, 1000)
+    got = classify_dev(torch_cuda, dp, hdr, ports)
+    assert np.all(got == np.uint64(consts.RESULT_MISS))
+
+
+def test_config2_full(torch_cuda):
+    """BASELINE.json configs[1]: 1K exact 5-tuple rules, 1M-packet batch."""
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    spec = config2_spec()
+    install_flows(sc, spec)
+    dp.commit()
+    n = 1 << 20
+    hdr, ports = gen_dev(torch_cuda, dp, spec, 0, n)
+    res = torch_cuda.zeros(n, dtype=torch_cuda.int64, device="cuda")
+    dp.classify(hdr.data_ptr(), ports.data_ptr(), res.data_ptr(), n, 0, torch_cuda.cuda.current_stream().cuda_stream)
+    torch_cuda.cuda.synchronize()
+    got = res.cpu().numpy().view(np.uint64)
+    want = sc.orc.classify(hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), threads=8)
+    assert_same(got, want)
+    stage = sfc.result_fields(got)[3]
+    hits = int((stage == consts.STAGE_FLOW).sum())
+    assert 0.85 * n < hits < 0.95 * n  # 90% of the traffic replays the rule set
+
+
+def test_config3_batches(torch_cuda):
+    """configs[2]: 1M-flow cuckoo table (IPv4 + IPv6), 4096-packet batches, 4-NF chain."""
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    topo = sc.build_chain(8, 4)
+    spec = config3_spec(n_flows=1 << 20, n_ports=topo["n_ports"])
+    install_flows(sc, spec)
+    dp.commit()
+    n_batches, b = 64, 4096
+    hdr, ports = gen_dev(torch_cuda, dp, spec, 0, n_batches * b)
+    res = torch_cuda.zeros(n_batches * b, dtype=torch_cuda.int64, device="cuda")
+    st = torch_cuda.cuda.current_stream().cuda_stream
+    for i in range(n_batches):  # one launch per batch
+        dp.classify(hdr.data_ptr() + i * b * 64, ports.data_ptr() + i * b * 2, res.data_ptr() + i * b * 8, b, 0, st)
+    torch_cuda.cuda.synchronize()
+    got = res.cpu().numpy().view(np.uint64)
+    want = sc.orc.classify(hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), threads=8)
+    assert_same(got, want)
+    stage = sfc.result_fields(got)[3]
+    for s in (consts.STAGE_FLOW, consts.STAGE_L2_EXACT, consts.STAGE_L2_WILD):
+        assert (stage == s).sum() > 0, f"stage {s} never hit"
+
+
+def test_config4_lpm_acl(torch_cuda):
+    """configs[3]: LPM (IPv4/IPv6) + ACL on 100K prefixes, mixed traffic."""
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    spec = config4_spec()
+    install_lpm_acl(sc, spec)
+    dp.commit()
+    n = 1 << 18  # the oracle's ACL is a linear scan of 1024 rules per packet
+    hdr, ports = gen_dev(torch_cuda, dp, spec, 0, n)
+    got = classify_dev(torch_cuda, dp, hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16))
+    want = sc.orc.classify(hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), threads=8)
+    assert_same(got, want, hdr.cpu().numpy())
+    stage = sfc.result_fields(got)[3]
+    for s in (consts.STAGE_ACL, consts.STAGE_LPM4, consts.STAGE_LPM6, consts.STAGE_MISS):
+        assert (stage == s).sum() > 0, f"stage {s} never hit"
+
+
+def test_everything_at_once_with_counters(torch_cuda):
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    topo = sc.build_chain(8, 2)
+    spec = config3_spec(n_flows=20000, n_ports=topo["n_ports"] + 4, n_pfx4=3000, n_pfx6=1000, lpm_permille=700,
+                        n_acl=300, hit_permille=600)
+    install_flows(sc, spec)
+    install_lpm_acl(sc, spec)
+    dp.commit()
+    n = 200000
+    hdr, ports = sfc.gen_packets_host(spec, 99, n)
+    got = classify_dev(torch_cuda, dp, hdr, ports, consts.F_COUNTERS)
+    want, cnt = sc.orc.classify(hdr, ports, counters=True)
+    assert_same(got, want, hdr)
+    assert np.array_equal(dp.counters_read(), cnt)
+    assert set(sfc.result_fields(got)[3].tolist()) == set(range(7))
+    dp.counters_reset()
+    assert dp.counters_read().sum() == 0
+
+
+def test_classify_host_matches_device_path(torch_cuda):
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    spec = config2_spec()
+    install_flows(sc, spec)
+    sc.build_chain(8, 1)
+    dp.commit()
+    n = (1 << 18) * 2 + 4321  # more than two staging chunks, ragged tail
+    hdr, ports = sfc.gen_packets_host(spec, 5, n)
+    got = dp.classify_host(hdr, ports)
+    assert_same(got, sc.orc.classify(hdr, ports, threads=8), hdr)
+    assert dp.last_kernel_ms > 0
+
+
+def test_rule_updates_between_commits(torch_cuda):
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    topo = sc.build_chain(4, 1)
+    spec = config2_spec(n_flows=2000, n_ports=topo["n_ports"])
+    install_flows(sc, spec)
+    dp.commit()
+    hdr, ports = sfc.gen_packets_host(spec, 0, 50000)
+    assert_same(classify_dev(torch_cuda, dp, hdr, ports), sc.orc.classify(hdr, ports), hdr)
+    # delete a VF the way DeleteBridgePort does (marvell/main.go:425-486), drop some flows, re-commit
+    vf = topo["vfs"][1]
+    sc.l2_del(vf, None)
+    sc.l2_del(topo["nf_out"][0], sfc.gen_mac(1))
+    sc.l2_del(topo["nf_in"][0], sfc.gen_mac(1))
+    keys, _ = sfc.gen_flows(spec, 0, 500)
+    for k in keys[::3]:
+        dp.flow_del(k)
+        sc.orc.flow_del(k)
+    e0 = dp.table_epoch
+    dp.commit()
+    assert dp.table_epoch == e0 + 1
+    assert_same(classify_dev(torch_cuda, dp, hdr, ports), sc.orc.classify(hdr, ports), hdr)
+
+
+def test_image_export_import_roundtrip(torch_cuda):
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    topo = sc.build_chain(8, 2)
+    spec = config3_spec(n_flows=30000, n_ports=topo["n_ports"])
+    install_flows(sc, spec)
+    dp.commit()
+    hdr, ports = sfc.gen_packets_host(spec, 0, 60000)
+    want = classify_dev(torch_cuda, dp, hdr, ports)
+    img = dp.table_export()
+    dp2 = sfc.Dataplane(0)
+    dp2.table_import(img)
+    assert_same(classify_dev(torch_cuda, dp2, hdr, ports), want)
+    # device-to-device path (what the NCCL broadcast uses)
+    buf = torch_cuda.empty(dp.table_size, dtype=torch_cuda.uint8, device="cuda")
+    dp.table_export_device(buf.data_ptr(), buf.numel())
+    torch_cuda.cuda.synchronize()
+    dp3 = sfc.Dataplane(0)
+    dp3.table_import_device(buf.data_ptr(), buf.numel())
+    assert_same(classify_dev(torch_cuda, dp3, hdr, ports), want)
+    with pytest.raises(sfc.SfcError):
+        dp2.table_import(img[:-256])
+
+
+def test_flow_roundtrip_property_16m(torch_cuda):
+    """Full-size property (configs[4] table): with 16M flows resident, every packet that replays
+    flow f must come back with rule index f and that flow's action — checked without the oracle by
+    regenerating flow f from the index the GPU returned."""
+    dp = sfc.Dataplane(0)
+    spec = config3_spec(n_flows=1 << 24, n_ports=8, nonip_permille=0, hit_permille=1000, zipf=0)
+    chunk = 1 << 20
+    for first in range(0, 1 << 24, chunk):
+        keys, acts = sfc.gen_flows(spec, first, chunk)
+        assert dp.flow_add_bulk(keys, acts) == first
+    dp.commit()
+    n = 1 << 22
+    hdr, ports = gen_dev(torch_cuda, dp, spec, 0, n)
+    res = torch_cuda.zeros(n, dtype=torch_cuda.int64, device="cuda")
+    dp.classify(hdr.data_ptr(), ports.data_ptr(), res.data_ptr(), n, 0, torch_cuda.cuda.current_stream().cuda_stream)
+    torch_cuda.cuda.synchronize()
+    got = res.cpu().numpy().view(np.uint64)
+    act, nf, port, stage, idx = sfc.result_fields(got)
+    hdr_h = hdr.cpu().numpy()
+    # fragments (1/256 of IPv4 packets) lose their ports by design and may miss; everything else hits
+    hit = stage == consts.STAGE_FLOW
+    assert hit.mean() > 0.99
+    sample = np.nonzero(hit)[0][:: max(1, hit.sum() // 200000)]
+    for i in sample[:20000]:
+        keys, acts = sfc.gen_flows(spec, int(idx[i]), 1)
+        p = Oracle.parse(hdr_h[i])
+        k = keys[0]
+        w = 4 if k["ip_ver"] == 4 else 16
+        assert (p["ver"], p["vlan"], p["proto"], p["sport"], p["dport"]) == (k["ip_ver"], k["vlan"], k["proto"], k["sport"], k["dport"])
+        assert p["src"][:w] == bytes(k["src"][:w]) and p["dst"][:w] == bytes(k["dst"][:w])
+        assert act[i] == acts[0]["action"] and port[i] == acts[0]["out_port"]
