@@ -150,6 +150,8 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--warm-seconds", type=float, default=0.3, help="minimum load time before the timed region (clock ramp)")
+    ap.add_argument("--no-clocks", action="store_true", help="skip nvidia-smi sampling (profiler runs)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -191,14 +193,14 @@ def main():
     # warm-up: W steps, and at least ~0.3 s of load so clocks have ramped before the timed region
     t_w = time.perf_counter()
     i = 0
-    while i < args.warmup or time.perf_counter() - t_w < 0.3:
+    while i < args.warmup or time.perf_counter() - t_w < args.warm_seconds:
         step(i)
         i += 1
         if i % 64 == 0:
             torch.cuda.synchronize()
     torch.cuda.synchronize()
 
-    sampler = ClockSampler(local) if rank == 0 else None
+    sampler = ClockSampler(local) if rank == 0 and not args.no_clocks else None
     launches0 = dp.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if world > 1:
