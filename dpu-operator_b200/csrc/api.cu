@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -42,7 +43,9 @@ struct sfc_handle {
     unsigned long long* d_counters = nullptr;
     uint64_t launches = 0;
     EncodeTiledFn encode = nullptr;
-    int ctas_per_sm[4] = {0, 0, 0, 0};
+    int ctas_per_sm[16] = {0};
+    int tune_tile = 0, tune_stages = 0;  // SFC_TUNE=tile,stages (experiments)
+    uint32_t flow_first[2] = {0, 0};
     // sfc_classify_host staging
     cudaStream_t hs[2] = {nullptr, nullptr};
     cudaEvent_t ev[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
@@ -92,8 +95,8 @@ void bind_tables(sfc_handle* h) {
     const uint8_t* b = h->d_image;
     T.flow4 = (const uint32_t*)(b + H.flow4_off);
     T.flow6 = (const uint32_t*)(b + H.flow6_off);
-    T.flow4_seed = H.flow4_seed;
-    T.flow6_seed = H.flow6_seed;
+    expand_seed(H.flow4_seed, T.S4, kFlow4SeedWords);
+    expand_seed(H.flow6_seed, T.S6, kFlow6SeedWords);
     T.flow4_nbuckets = H.flow4_nbuckets;
     T.flow4_nhash = H.flow4_nhash;
     T.flow4_count = H.flow4_count;
@@ -106,15 +109,13 @@ void bind_tables(sfc_handle* h) {
     T.l2w = (const L2Wild*)(b + H.l2w_off);
     T.l2w_n = H.l2w_n;
     T.l2w_count = H.l2w_count;
-    T.nf = b + H.nf_off;
-    T.nf_n = H.nf_n;
     T.lpm4_root = (const uint32_t*)(b + H.lpm4_root_off);
     T.lpm4_nodes = (const uint32_t*)(b + H.lpm4_nodes_off);
-    T.lpm4_nh = (const uint16_t*)(b + H.lpm4_nh_off);
+    T.lpm4_nh = (const LpmRes*)(b + H.lpm4_nh_off);
     T.lpm4_count = H.lpm4_count;
     T.lpm6_root = (const uint32_t*)(b + H.lpm6_root_off);
     T.lpm6_nodes = (const uint32_t*)(b + H.lpm6_nodes_off);
-    T.lpm6_nh = (const uint16_t*)(b + H.lpm6_nh_off);
+    T.lpm6_nh = (const LpmRes*)(b + H.lpm6_nh_off);
     T.lpm6_count = H.lpm6_count;
     T.acl_bv = (const uint32_t*)(b + H.acl_bv_off);
     T.acl_base = (const uint32_t*)(b + H.acl_base_off);
@@ -129,6 +130,8 @@ void bind_tables(sfc_handle* h) {
     memcpy(T.acl_slot6, H.acl_slot6, kAclMaxPos);
     T.counters = h->d_counters;
     h->epoch = H.epoch;
+    h->flow_first[0] = H.flow4_first;
+    h->flow_first[1] = H.flow6_first;
 }
 
 int install_image_from_host(sfc_handle* h, const uint8_t* img, size_t len) {
@@ -147,26 +150,30 @@ int install_image_from_host(sfc_handle* h, const uint8_t* img, size_t len) {
     return 0;
 }
 
-template <bool C, bool A>
-auto kernel_ptr() {
-    return classify_kernel<kTile, kStages, C, A>;
-}
-
-template <bool C, bool A>
-int launch_variant(sfc_handle* h, int variant, const CUtensorMap& map, const uint16_t* in_port, uint64_t* result,
-                   size_t n, cudaStream_t st) {
-    auto kern = kernel_ptr<C, A>();
-    constexpr int smem = SmemLayout<kTile, kStages>::kBytes;
-    if (!h->ctas_per_sm[variant]) {
+template <int TILE, int STAGES, bool C, bool A>
+int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
+                   cudaStream_t st) {
+    auto kern = classify_kernel<TILE, STAGES, C, A>;
+    constexpr int smem = SmemLayout<TILE, STAGES, A>::kBytes;
+    if (!h->ctas_per_sm[slot]) {
         CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         int per = 0;
-        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, kern, kTile + 32, smem));
+        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, kern, TILE + 32, smem));
         if (per < 1) return fail(h, -EIO, "classify kernel does not fit on an SM");
-        h->ctas_per_sm[variant] = per;
+        h->ctas_per_sm[slot] = per;
     }
-    uint64_t n_tiles = (n + kTile - 1) / kTile;
-    uint64_t grid = std::min<uint64_t>(n_tiles, (uint64_t)h->sm_count * h->ctas_per_sm[variant]);
-    kern<<<(unsigned)grid, kTile + 32, smem, st>>>(map, in_port, result, (uint64_t)n, (uint32_t)n_tiles, h->T);
+    CUtensorMap map;
+    cuuint64_t dims[2] = {16, (cuuint64_t)n};  // 16 x u32 per record, n records
+    cuuint64_t strides[1] = {64};
+    cuuint32_t box[2] = {16, (cuuint32_t)(TILE < 256 ? TILE : 256)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = h->encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(hdr), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(h, -EIO, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    uint64_t n_tiles = (n + TILE - 1) / TILE;
+    uint64_t grid = std::min<uint64_t>(n_tiles, (uint64_t)h->sm_count * h->ctas_per_sm[slot]);
+    kern<<<(unsigned)grid, TILE + 32, smem, st>>>(map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, h->T);
     CUDA_TRY(h, cudaGetLastError());
     ++h->launches;
     return 0;
@@ -177,20 +184,25 @@ int launch_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uin
     if (!h->d_image) return fail(h, -EINVAL, "sfc_classify: no committed table image (call sfc_commit)");
     if (((uintptr_t)hdr & 15) != 0) return fail(h, -EINVAL, "sfc_classify: hdr must be 16-byte aligned");
     if (n > (1ull << 31)) return fail(h, -EINVAL, "sfc_classify: at most 2^31 packets per call");
-    CUtensorMap map;
-    cuuint64_t dims[2] = {16, (cuuint64_t)n};  // 16 x u32 per record, n records
-    cuuint64_t strides[1] = {64};
-    cuuint32_t box[2] = {16, (cuuint32_t)kTile};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = h->encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(hdr), dims, strides, box, estr,
-                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail(h, -EIO, "cuTensorMapEncodeTiled failed (%d)", (int)r);
     bool c = flags & SFC_F_COUNTERS, a = h->T.acl_nrules > 0;
-    if (c && a) return launch_variant<true, true>(h, 3, map, in_port, result, n, st);
-    if (c) return launch_variant<true, false>(h, 2, map, in_port, result, n, st);
-    if (a) return launch_variant<false, true>(h, 1, map, in_port, result, n, st);
-    return launch_variant<false, false>(h, 0, map, in_port, result, n, st);
+    if (!c && !a && h->tune_tile) {  // experiment hook: SFC_TUNE=tile,stages
+#define SFC_TUNE_CASE(slot, T_, S_) \
+    if (h->tune_tile == T_ && h->tune_stages == S_) return launch_variant<T_, S_, false, false>(h, slot, hdr, in_port, result, n, st);
+        SFC_TUNE_CASE(4, 64, 4)
+        SFC_TUNE_CASE(5, 128, 2)
+        SFC_TUNE_CASE(6, 128, 3)
+        SFC_TUNE_CASE(7, 256, 2)
+        SFC_TUNE_CASE(8, 256, 3)
+        SFC_TUNE_CASE(9, 256, 4)
+        SFC_TUNE_CASE(10, 512, 2)
+        SFC_TUNE_CASE(11, 512, 3)
+        SFC_TUNE_CASE(12, 768, 2)
+#undef SFC_TUNE_CASE
+    }
+    if (c && a) return launch_variant<kTile, kStages, true, true>(h, 3, hdr, in_port, result, n, st);
+    if (c) return launch_variant<kTile, kStages, true, false>(h, 2, hdr, in_port, result, n, st);
+    if (a) return launch_variant<kTile, kStages, false, true>(h, 1, hdr, in_port, result, n, st);
+    return launch_variant<kTile, kStages, false, false>(h, 0, hdr, in_port, result, n, st);
 }
 
 __global__ void gen_kernel(sfc_gen_spec spec, uint64_t first, uint64_t n, uint8_t* hdr, uint16_t* in_port) {
@@ -241,6 +253,7 @@ int sfc_create(int device_ordinal, sfc_handle** out) {
         return -ENOSYS;
     }
     h->encode = (EncodeTiledFn)fn;
+    if (const char* tune = getenv("SFC_TUNE")) sscanf(tune, "%d,%d", &h->tune_tile, &h->tune_stages);
     if (cudaMalloc(&h->d_counters, SFC_CNT_TOTAL * sizeof(uint64_t)) != cudaSuccess ||
         cudaMemset(h->d_counters, 0, SFC_CNT_TOTAL * sizeof(uint64_t)) != cudaSuccess) {
         delete h;
@@ -284,6 +297,14 @@ int sfc_set_option(sfc_handle* h, const char* name, long value) {
     if (!strcmp(name, "flow_hashes")) {
         if (value < 2 || value > kMaxHashes) return fail(h, -EINVAL, "flow_hashes must be 2 or 3");
         h->rs.flow_hashes = (int)value;
+        return 0;
+    }
+    if (!strcmp(name, "tune_tile")) {  // experiment hooks: pick a compiled (tile, stages) variant
+        h->tune_tile = (int)value;
+        return 0;
+    }
+    if (!strcmp(name, "tune_stages")) {
+        h->tune_stages = (int)value;
         return 0;
     }
     return fail(h, -ENOENT, "unknown option '%s'", name);

@@ -19,22 +19,21 @@ namespace sfc {
 struct DevTables {
     const uint32_t* flow4;
     const uint32_t* flow6;
-    uint64_t flow4_seed, flow6_seed;
     uint32_t flow4_nbuckets, flow4_nhash, flow4_count;
     uint32_t flow6_nbuckets, flow6_nhash, flow6_count;
+    uint32_t S4[kFlow4SeedWords];
+    uint32_t S6[kFlow6SeedWords];
     const L2Entry* l2x;
     uint32_t l2x_mask, l2x_count;
     const L2Wild* l2w;
     uint32_t l2w_n, l2w_count;
-    const uint8_t* nf;
-    uint32_t nf_n;
     const uint32_t* lpm4_root;
     const uint32_t* lpm4_nodes;
-    const uint16_t* lpm4_nh;
+    const LpmRes* lpm4_nh;
     uint32_t lpm4_count;
     const uint32_t* lpm6_root;
     const uint32_t* lpm6_nodes;
-    const uint16_t* lpm6_nh;
+    const LpmRes* lpm6_nh;
     uint32_t lpm6_count;
     const uint32_t* acl_bv;
     const uint32_t* acl_base;  // [2][nwords]
@@ -91,8 +90,8 @@ __device__ __forceinline__ void ldg256(const void* p, uint32_t* r) {
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "l"(p));
 }
-__device__ __forceinline__ void stg_result(uint64_t* p, uint64_t v) {
-    asm volatile("st.global.cs.b64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+__device__ __forceinline__ void stg_result(uint64_t* p, uint32_t lo, uint32_t hi) {
+    asm volatile("st.global.cs.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(lo), "r"(hi) : "memory");
 }
 __device__ __forceinline__ uint32_t be32_pair(uint32_t lo_word, uint32_t hi_word) {
     // big-endian value of the 4 bytes that start at byte 2 of lo_word
@@ -108,8 +107,6 @@ __device__ __forceinline__ uint32_t word_at(const uint32_t* w, int i) {  // dyna
 // ------------------------------------------------------------------ stage 0: parse -------
 // w[16]: the record as little-endian words.  Fills k; returns false for non-IP frames.
 __device__ __forceinline__ bool parse_header(uint32_t* w, Key& k) {
-    k.mac_hi = __byte_perm(w[0], 0, 0x4401);  // bytes 0,1 big-endian
-    k.mac_lo = be32_pair(w[0], w[1]);
     uint32_t et = __byte_perm(w[3], 0, 0x4401);
     uint32_t vlan = 0;
     int limit = 64;
@@ -164,41 +161,51 @@ __device__ __forceinline__ bool parse_header(uint32_t* w, Key& k) {
 }
 
 // ------------------------------------------------------------------ stage 2: flows -------
-__device__ __forceinline__ bool flow4_lookup(const DevTables& T, const Key& k, uint32_t& m0, uint32_t& m1) {
-    uint32_t meta20 = k.meta & 0xFFFFFu;
-    uint64_t d = flow4_digest(k.sip[0], k.dip[0], k.ports, meta20, T.flow4_seed);
-    for (uint32_t j = 0; j < T.flow4_nhash; ++j) {
-        uint32_t b = flow_bucket(d, (int)j, T.flow4_nbuckets);
-        uint32_t s[8];
-        ldg256(T.flow4 + (size_t)b * (kFlow4BucketBytes / 4), s);
-        if (s[0] == k.sip[0] && s[1] == k.dip[0] && s[2] == k.ports && (s[3] & 0xFFFFFu) == meta20 &&
-            slot_action(s[3]) != 3u) {
-            m0 = s[3];
-            m1 = s[4];
-            return true;
+// One 32-byte sector per probe; the first-choice bucket holds most flows (the builder reports how
+// many), so the second load is predicated on a miss instead of being issued up front.
+__device__ __forceinline__ bool flow4_lookup(const DevTables& T, const Key& k, uint32_t& rhi, uint32_t& rlo) {
+    const uint32_t meta20 = k.meta & 0xFFFFFu, tag = meta20 | kSlotValid;
+    uint32_t x, y;
+    flow4_hash(k.sip[0], k.dip[0], k.ports, meta20, T.S4, x, y);
+    const uint32_t b0 = flow_bucket(x, y, 0, T.S4 + 4, T.flow4_nbuckets);
+    const uint32_t b1 = flow_bucket(x, y, 1, T.S4 + 4, T.flow4_nbuckets);
+    uint32_t s[8];
+    ldg256(T.flow4 + (size_t)b0 * kFlow4BucketWords, s);
+    bool hit = s[0] == k.sip[0] && s[1] == k.dip[0] && s[2] == k.ports && s[3] == tag;
+    if (!hit) {
+        ldg256(T.flow4 + (size_t)b1 * kFlow4BucketWords, s);
+        hit = s[0] == k.sip[0] && s[1] == k.dip[0] && s[2] == k.ports && s[3] == tag;
+        if (!hit && T.flow4_nhash > 2) {
+            const uint32_t b2 = flow_bucket(x, y, 2, T.S4 + 4, T.flow4_nbuckets);
+            ldg256(T.flow4 + (size_t)b2 * kFlow4BucketWords, s);
+            hit = s[0] == k.sip[0] && s[1] == k.dip[0] && s[2] == k.ports && s[3] == tag;
         }
     }
-    return false;
+    rhi = s[4];
+    rlo = s[5];
+    return hit;
 }
-__device__ __forceinline__ bool flow6_lookup(const DevTables& T, const Key& k, uint32_t& m0, uint32_t& m1) {
-    uint32_t meta20 = k.meta & 0xFFFFFu;
-    uint64_t d = flow6_digest(k.sip, k.dip, k.ports, meta20, T.flow6_seed);
-    for (uint32_t j = 0; j < T.flow6_nhash; ++j) {
-        uint32_t b = flow_bucket(d, (int)j, T.flow6_nbuckets);
-        const uint32_t* p = T.flow6 + (size_t)b * (kFlow6BucketBytes / 4);
-        uint32_t s[16];
-        ldg256(p, s);
-        ldg256(p + 8, s + 8);
-        bool eq = (s[8] == k.ports) && ((s[9] & 0xFFFFFu) == meta20) && slot_action(s[9]) != 3u;
+__device__ __forceinline__ bool flow6_probe(const uint32_t* p, const Key& k, uint32_t tag, uint32_t& rhi, uint32_t& rlo) {
+    uint32_t s[16];
+    ldg256(p, s);
+    ldg256(p + 8, s + 8);
+    bool eq = s[8] == k.ports && s[9] == tag;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) eq = eq && s[i] == k.sip[i] && s[4 + i] == k.dip[i];
-        if (eq) {
-            m0 = s[9];
-            m1 = s[10];
-            return true;
-        }
+    for (int i = 0; i < 4; ++i) eq = eq && s[i] == k.sip[i] && s[4 + i] == k.dip[i];
+    rhi = s[10];
+    rlo = s[11];
+    return eq;
+}
+__device__ __forceinline__ bool flow6_lookup(const DevTables& T, const Key& k, uint32_t& rhi, uint32_t& rlo) {
+    const uint32_t meta20 = k.meta & 0xFFFFFu, tag = meta20 | kSlotValid;
+    uint32_t x, y;
+    flow6_hash(k.sip, k.dip, k.ports, meta20, T.S6, x, y);
+    bool hit = false;
+    for (uint32_t j = 0; j < T.flow6_nhash && !hit; ++j) {
+        uint32_t b = flow_bucket(x, y, (int)j, T.S6 + 10, T.flow6_nbuckets);
+        hit = flow6_probe(T.flow6 + (size_t)b * kFlow6BucketWords, k, tag, rhi, rlo);
     }
-    return false;
+    return hit;
 }
 
 // ------------------------------------------------------------------ stage 4: LPM ---------
@@ -215,34 +222,33 @@ __device__ __forceinline__ uint32_t lpm_lookup(const uint32_t* __restrict__ root
     return (e & kLpmChild) ? 0u : e;
 }
 
-__device__ __forceinline__ uint32_t nf_of(const DevTables& T, uint32_t port) {
-    return port < T.nf_n ? (uint32_t)__ldg(T.nf + port) : (uint32_t)SFC_NF_NONE;
-}
-
 // ------------------------------------------------------------------ the kernel -----------
-template <int TILE, int STAGES>
+template <int TILE, int STAGES, bool ACL>
 struct SmemLayout {
     static constexpr int kTileBytes = TILE * 64;
-    static constexpr int kAclBytes = (TILE / 32) * kAclKeyWords * 32 * 4;
-    static constexpr int kBytes = STAGES * kTileBytes + kAclBytes + 2 * STAGES * 8 + 16 * 8 + 1024;
+    static constexpr int kAclBytes = ACL ? (TILE / 32) * kAclKeyWords * 32 * 4 : 0;
+    static constexpr int kBytes = STAGES * kTileBytes + kAclBytes + 2 * STAGES * 8 + 16 * 8 + 32 * 4 + 1024;
 };
 
 template <int TILE, int STAGES, bool COUNTERS, bool ACL>
 __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
                                                               const uint16_t* __restrict__ in_port,
-                                                              uint64_t* __restrict__ result, uint64_t n,
+                                                              uint64_t* __restrict__ result, uint32_t n,
                                                               uint32_t n_tiles,
                                                               const __grid_constant__ DevTables T) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* tiles = smem;
     uint32_t* aclq = (uint32_t*)(smem + STAGES * TILE * 64);
-    uint64_t* full = (uint64_t*)((uint8_t*)aclq + SmemLayout<TILE, STAGES>::kAclBytes);
+    uint64_t* full = (uint64_t*)((uint8_t*)aclq + SmemLayout<TILE, STAGES, ACL>::kAclBytes);
     uint64_t* empty = full + STAGES;
     unsigned long long* scnt = (unsigned long long*)(empty + STAGES);  // 16 block-level counters
+    uint32_t* dep_sink = (uint32_t*)(scnt + 16);                       // one word per consumer warp
 
     const int tid = threadIdx.x;
     constexpr int kConsumerWarps = TILE / 32;
+    constexpr int kBoxRows = TILE < 256 ? TILE : 256;
+    static_assert(TILE % kBoxRows == 0, "TILE must be a multiple of the TMA box height");
     if (tid == 0) {
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(full + s, 1);
@@ -262,174 +268,191 @@ __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_consta
                 uint32_t s = it % STAGES, use = it / STAGES;
                 if (use > 0) mbar_wait(empty + s, (use - 1) & 1);
                 mbar_arrive_expect_tx(full + s, TILE * 64);
-                tma_load_tile(tiles + s * TILE * 64, &hdr_map, 0, (int)(tile * TILE), full + s, pol);
+#pragma unroll
+                for (int r = 0; r < TILE; r += kBoxRows)  // a TMA box is at most 256 rows
+                    tma_load_tile(tiles + s * TILE * 64 + r * 64, &hdr_map, 0, (int)(tile * TILE) + r, full + s, pol);
             }
         }
-    } else {
-        // ---------------- consumers: one packet per thread per tile ----------------
-        const int lane = tid & 31, warp = tid >> 5;
-        const uint32_t row_off = (uint32_t)tid * 64u;
-        const uint32_t sw = ((uint32_t)tid >> 1) & 3u;
-        uint32_t it = 0;
-        for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-            uint32_t s = it % STAGES, use = it / STAGES;
-            uint64_t pkt = (uint64_t)tile * TILE + tid;
-            bool live = pkt < n;
-            uint32_t port = live ? (uint32_t)__ldg(in_port + pkt) : 0u;
+        return;
+    }
+    // ---------------- consumers: one packet per thread per tile ----------------
+    const int lane = tid & 31;
+    const uint32_t row_off = (uint32_t)tid * 64u;
+    const uint32_t sw = ((uint32_t)tid >> 1) & 3u;
+    uint32_t it = 0;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        const uint32_t s = it % STAGES, use = it / STAGES;
+        const uint32_t pkt = tile * TILE + tid;
+        const bool live = pkt < n;
+        const uint32_t port = live ? (uint32_t)__ldg(in_port + pkt) : 0u;
 
-            mbar_wait(full + s, use & 1);
-            uint32_t w[16];
-            uint32_t base = smem_u32(tiles + s * TILE * 64) + row_off;
+        mbar_wait(full + s, use & 1);
+        uint32_t w[16];
+        const uint32_t base = smem_u32(tiles + s * TILE * 64) + row_off;
 #pragma unroll
-            for (uint32_t c = 0; c < 4; ++c) {
-                uint4 v = lds128(base + ((c ^ sw) << 4));
-                w[4 * c + 0] = v.x;
-                w[4 * c + 1] = v.y;
-                w[4 * c + 2] = v.z;
-                w[4 * c + 3] = v.w;
+        for (uint32_t c = 0; c < 4; ++c) {
+            uint4 v = lds128(base + ((c ^ sw) << 4));
+            w[4 * c + 0] = v.x;
+            w[4 * c + 1] = v.y;
+            w[4 * c + 2] = v.z;
+            w[4 * c + 3] = v.w;
+        }
+        // Release the slot as soon as the record sits in registers.  "Sits in registers" must be
+        // enforced: LDS data returns asynchronously, and under load the arrive below can overtake
+        // it, letting the producer's next TMA overwrite rows that have not been read yet (seen on
+        // B200 as sporadic wrong rows).  Folding one word of each of the four loads into a value
+        // that lane 0 stores makes the store — issued in order before the arrive — wait on the
+        // warp-wide scoreboard of all four LDS instructions.
+        const uint32_t dep = w[3] ^ w[7] ^ w[11] ^ w[15];
+        __syncwarp();
+        if (lane == 0) {
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(smem_u32(dep_sink + (tid >> 5))), "r"(dep) : "memory");
+            mbar_arrive(empty + s);
+        }
+
+        // dst MAC first: parse_header may slide the words of a tagged frame
+        const uint32_t mac_hi = __byte_perm(w[0], 0, 0x4401), mac_lo = be32_pair(w[0], w[1]);
+        Key k;
+        const bool is_ip = parse_header(w, k);
+        uint32_t rhi = kResMissHi, rlo = kResMissLo;
+        bool done = !live;  // lanes past the end of the batch hold zero-filled records
+
+        // ---- stage 1: ACL (warp-cooperative byte-sliced bit vectors) ----
+        if (ACL) {
+            uint32_t* q = aclq + (tid >> 5) * (kAclKeyWords * 32);
+            q[0 * 32 + lane] = (port << 16) | (k.meta >> 8);
+            q[1 * 32 + lane] = (k.ip_ver << 24) | ((k.meta & 0xFFu) << 16) | (k.ports >> 16);
+            q[2 * 32 + lane] = k.ports << 16;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                q[(3 + i) * 32 + lane] = k.sip[i];
+                q[(7 + i) * 32 + lane] = k.dip[i];
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(empty + s);
-
-            Key k;
-            bool is_ip = parse_header(w, k);
-            uint64_t res = SFC_RESULT_MISS;
-            bool done = !live;  // lanes past the end of the batch hold zero-filled records
-
-            // ---- stage 1: ACL (warp-cooperative byte-sliced bit vectors) ----
-            if (ACL) {
-                uint32_t* q = aclq + warp * (kAclKeyWords * 32);
-                q[0 * 32 + lane] = (port << 16) | (k.meta >> 8);
-                q[1 * 32 + lane] = (k.ip_ver << 24) | ((k.meta & 0xFFu) << 16) | (k.ports >> 16);
-                q[2 * 32 + lane] = k.ports << 16;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    q[(3 + i) * 32 + lane] = k.sip[i];
-                    q[(7 + i) * 32 + lane] = k.dip[i];
-                }
-                __syncwarp();
-                uint32_t todo = __ballot_sync(0xFFFFFFFFu, live && is_ip);
-                uint32_t my_hit = 0xFFFFFFFFu;
-                while (todo) {
-                    int j = __ffs(todo) - 1;
-                    todo &= todo - 1;
-                    bool v6 = (q[1 * 32 + j] >> 24) == 6u;
-                    const uint8_t* pos = v6 ? T.acl_pos6 : T.acl_pos4;
-                    const uint8_t* slot = v6 ? T.acl_slot6 : T.acl_slot4;
-                    uint32_t npos = v6 ? T.acl_npos6 : T.acl_npos4;
-                    uint32_t best = 0xFFFFFFFFu;
-                    for (uint32_t wbase = 0; wbase < T.acl_nwords && best == 0xFFFFFFFFu; wbase += 32) {
-                        uint32_t wi = wbase + lane;
-                        bool in = wi < T.acl_nwords;
-                        uint32_t acc = in ? __ldg(T.acl_base + (v6 ? T.acl_nwords : 0) + wi) : 0u;
-                        for (uint32_t p = 0; p < npos; ++p) {
-                            uint32_t kb = pos[p];
-                            uint32_t val = (q[(kb >> 2) * 32 + j] >> (24 - 8 * (kb & 3))) & 0xFFu;
-                            if (in) acc &= __ldg(T.acl_bv + ((size_t)slot[p] * 256 + val) * T.acl_nwords + wi);
-                            if ((p & 3) == 3 && __ballot_sync(0xFFFFFFFFu, acc != 0) == 0) break;
-                        }
-                        uint32_t any = __ballot_sync(0xFFFFFFFFu, acc != 0);
-                        if (any) {
-                            int src = __ffs(any) - 1;
-                            uint32_t word = __shfl_sync(0xFFFFFFFFu, acc, src);
-                            best = (wbase + src) * 32 + (__ffs(word) - 1);
-                        }
+            uint32_t todo = __ballot_sync(0xFFFFFFFFu, live && is_ip);
+            uint32_t my_hit = 0xFFFFFFFFu;
+            while (todo) {
+                int j = __ffs(todo) - 1;
+                todo &= todo - 1;
+                bool v6 = (q[1 * 32 + j] >> 24) == 6u;
+                const uint8_t* pos = v6 ? T.acl_pos6 : T.acl_pos4;
+                const uint8_t* slot = v6 ? T.acl_slot6 : T.acl_slot4;
+                uint32_t npos = v6 ? T.acl_npos6 : T.acl_npos4;
+                uint32_t best = 0xFFFFFFFFu;
+                for (uint32_t wbase = 0; wbase < T.acl_nwords && best == 0xFFFFFFFFu; wbase += 32) {
+                    uint32_t wi = wbase + lane;
+                    bool in = wi < T.acl_nwords;
+                    uint32_t acc = in ? __ldg(T.acl_base + (v6 ? T.acl_nwords : 0) + wi) : 0u;
+                    for (uint32_t p = 0; p < npos; ++p) {
+                        uint32_t kb = pos[p];
+                        uint32_t val = (q[(kb >> 2) * 32 + j] >> (24 - 8 * (kb & 3))) & 0xFFu;
+                        if (in) acc &= __ldg(T.acl_bv + ((size_t)slot[p] * 256 + val) * T.acl_nwords + wi);
+                        if ((p & 3) == 3 && __ballot_sync(0xFFFFFFFFu, acc != 0) == 0) break;
                     }
-                    if (lane == j) my_hit = best;
-                }
-                __syncwarp();
-                if (my_hit != 0xFFFFFFFFu) {
-                    uint32_t r = __ldg(T.acl_rule + my_hit);
-                    if (COUNTERS) atomicAdd(T.counters + SFC_CNT_RULES0 + (r & 0x0FFFFFFFu), 1ull);
-                    if (r & 0x80000000u) {
-                        res = SFC_RESULT(SFC_ACT_DROP, SFC_NF_NONE, 0, SFC_STAGE_ACL, r & 0x0FFFFFFFu);
-                        done = true;
+                    uint32_t any = __ballot_sync(0xFFFFFFFFu, acc != 0);
+                    if (any) {
+                        int src = __ffs(any) - 1;
+                        uint32_t word = __shfl_sync(0xFFFFFFFFu, acc, src);
+                        best = (wbase + src) * 32 + (__ffs(word) - 1);
                     }
                 }
+                if (lane == j) my_hit = best;
             }
-
-            // ---- stage 2: exact 5-tuple ----
-            if (!done && is_ip) {
-                uint32_t m0 = 0, m1 = 0;
-                bool hit = false;
-                if (k.ip_ver == 4) {
-                    if (T.flow4_count) hit = flow4_lookup(T, k, m0, m1);
-                } else if (T.flow6_count) {
-                    hit = flow6_lookup(T, k, m0, m1);
-                }
-                if (hit) {
-                    uint32_t act = slot_action(m0), op = slot_port(m1);
-                    uint32_t nf = act == SFC_ACT_FORWARD ? nf_of(T, op) : (uint32_t)SFC_NF_NONE;
-                    res = SFC_RESULT(act, nf, op, SFC_STAGE_FLOW, slot_id(m0, m1));
+            __syncwarp();
+            if (my_hit != 0xFFFFFFFFu) {
+                uint32_t r = __ldg(T.acl_rule + my_hit);
+                if (COUNTERS) atomicAdd(T.counters + SFC_CNT_RULES0 + (r & 0x0FFFFFFFu), 1ull);
+                if (r & 0x80000000u) {
+                    rhi = res_hi(SFC_ACT_DROP, SFC_NF_NONE, 0);
+                    rlo = res_lo(SFC_STAGE_ACL, r);
                     done = true;
                 }
             }
+        }
 
-            // ---- stage 3: SFC L2 steering ----
-            if (!done) {
-                if (T.l2x_count) {
-                    uint32_t key_hi = (port << 16) | k.mac_hi;
-                    uint32_t i = l2_hash(key_hi, k.mac_lo) & T.l2x_mask;
-                    for (;;) {
-                        uint4 e = __ldg(reinterpret_cast<const uint4*>(T.l2x + i));
-                        if (!(e.w & 0x80000000u)) break;
-                        if (e.x == k.mac_lo && e.y == key_hi) {
-                            uint32_t op = e.w & 0xFFFFu;
-                            res = SFC_RESULT(SFC_ACT_FORWARD, nf_of(T, op), op, SFC_STAGE_L2_EXACT, e.z);
-                            done = true;
-                            if (COUNTERS) atomicAdd(T.counters + SFC_CNT_L2_0 + (e.z % SFC_CNT_L2_N), 1ull);
-                            break;
-                        }
-                        i = (i + 1) & T.l2x_mask;
-                    }
-                }
-                if (!done && T.l2w_count && port < T.l2w_n) {
-                    uint2 e = __ldg(reinterpret_cast<const uint2*>(T.l2w + port));
-                    if (e.x & 0x80000000u) {
-                        uint32_t op = e.x & 0xFFFFu;
-                        res = SFC_RESULT(SFC_ACT_FORWARD, nf_of(T, op), op, SFC_STAGE_L2_WILD, e.y);
+        // ---- stage 2: exact 5-tuple ----
+        if (!done && is_ip) {
+            uint32_t h = 0, l = 0;
+            bool hit = false;
+            if (k.ip_ver == 4) {
+                if (T.flow4_count) hit = flow4_lookup(T, k, h, l);
+            } else if (T.flow6_count) {
+                hit = flow6_lookup(T, k, h, l);
+            }
+            if (hit) {
+                rhi = h;
+                rlo = l;
+                done = true;
+            }
+        }
+
+        // ---- stage 3: SFC L2 steering ----
+        if (!done) {
+            if (T.l2x_count) {
+                uint32_t key_hi = (port << 16) | mac_hi;
+                uint32_t i = l2_hash(key_hi, mac_lo) & T.l2x_mask;
+                for (;;) {
+                    uint4 e = __ldg(reinterpret_cast<const uint4*>(T.l2x + i));
+                    if (!e.w) break;
+                    if (e.x == mac_lo && e.y == key_hi) {
+                        rlo = e.z;
+                        rhi = e.w;
                         done = true;
-                        if (COUNTERS) atomicAdd(T.counters + SFC_CNT_L2_0 + (e.y % SFC_CNT_L2_N), 1ull);
+                        if (COUNTERS) atomicAdd(T.counters + SFC_CNT_L2_0 + ((e.z & 0x0FFFFFFFu) % SFC_CNT_L2_N), 1ull);
+                        break;
                     }
+                    i = (i + 1) & T.l2x_mask;
                 }
             }
-
-            // ---- stage 4: LPM on the destination ----
-            if (!done && is_ip) {
-                if (k.ip_ver == 4 && T.lpm4_count) {
-                    uint32_t e = lpm_lookup<32>(T.lpm4_root, T.lpm4_nodes, k.dip);
-                    if (e) {
-                        uint32_t op = __ldg(T.lpm4_nh + (e - 1));
-                        res = SFC_RESULT(SFC_ACT_FORWARD, nf_of(T, op), op, SFC_STAGE_LPM4, e - 1);
-                    }
-                } else if (k.ip_ver == 6 && T.lpm6_count) {
-                    uint32_t e = lpm_lookup<128>(T.lpm6_root, T.lpm6_nodes, k.dip);
-                    if (e) {
-                        uint32_t op = __ldg(T.lpm6_nh + (e - 1));
-                        res = SFC_RESULT(SFC_ACT_FORWARD, nf_of(T, op), op, SFC_STAGE_LPM6, e - 1);
-                    }
+            if (!done && T.l2w_count && port < T.l2w_n) {
+                uint2 e = __ldg(reinterpret_cast<const uint2*>(T.l2w + port));
+                if (e.x) {
+                    rhi = e.x;
+                    rlo = e.y;
+                    done = true;
+                    if (COUNTERS) atomicAdd(T.counters + SFC_CNT_L2_0 + ((e.y & 0x0FFFFFFFu) % SFC_CNT_L2_N), 1ull);
                 }
             }
+        }
 
-            if (live) stg_result(result + pkt, res);
+        // ---- stage 4: LPM on the destination ----
+        if (!done && is_ip) {
+            if (k.ip_ver == 4 && T.lpm4_count) {
+                uint32_t e = lpm_lookup<32>(T.lpm4_root, T.lpm4_nodes, k.dip);
+                if (e) {
+                    uint2 r = __ldg(reinterpret_cast<const uint2*>(T.lpm4_nh + (e - 1)));
+                    rhi = r.x;
+                    rlo = r.y;
+                }
+            } else if (k.ip_ver == 6 && T.lpm6_count) {
+                uint32_t e = lpm_lookup<128>(T.lpm6_root, T.lpm6_nodes, k.dip);
+                if (e) {
+                    uint2 r = __ldg(reinterpret_cast<const uint2*>(T.lpm6_nh + (e - 1)));
+                    rhi = r.x;
+                    rlo = r.y;
+                }
+            }
+        }
 
-            if (COUNTERS) {
-                uint32_t act = SFC_RESULT_ACTION(res), stage = SFC_RESULT_STAGE(res);
+        if (live) stg_result(result + pkt, rlo, rhi);
+
+        if (COUNTERS) {
+            uint32_t act = rhi >> 24, stage = rlo >> 28;
 #pragma unroll
-                for (uint32_t a = 0; a < 3; ++a) {
-                    uint32_t m = __ballot_sync(0xFFFFFFFFu, live && act == a);
-                    if (lane == 0 && m) atomicAdd(scnt + SFC_CNT_ACTION0 + a, (unsigned long long)__popc(m));
-                }
+            for (uint32_t a = 0; a < 3; ++a) {
+                uint32_t m = __ballot_sync(0xFFFFFFFFu, live && act == a);
+                if (lane == 0 && m) atomicAdd(scnt + SFC_CNT_ACTION0 + a, (unsigned long long)__popc(m));
+            }
 #pragma unroll
-                for (uint32_t st = 0; st < 7; ++st) {
-                    uint32_t m = __ballot_sync(0xFFFFFFFFu, live && stage == st);
-                    if (lane == 0 && m) atomicAdd(scnt + SFC_CNT_STAGE0 + st, (unsigned long long)__popc(m));
-                }
+            for (uint32_t st = 0; st < 7; ++st) {
+                uint32_t m = __ballot_sync(0xFFFFFFFFu, live && stage == st);
+                if (lane == 0 && m) atomicAdd(scnt + SFC_CNT_STAGE0 + st, (unsigned long long)__popc(m));
             }
         }
     }
     if (COUNTERS) {
-        __syncthreads();
+        // consumers only (the producer warp has left): named barrier over the TILE consumer threads
+        asm volatile("bar.sync 1, %0;" ::"n"(TILE));
         if (tid < 16 && scnt[tid]) atomicAdd(T.counters + tid, scnt[tid]);
     }
 }

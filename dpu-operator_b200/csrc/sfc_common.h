@@ -4,6 +4,8 @@
 #pragma once
 #include <stdint.h>
 
+#include "../../include/b200sfc.h"
+
 #if defined(__CUDACC__)
 #define SFC_HD __host__ __device__ __forceinline__
 #else
@@ -41,76 +43,83 @@ struct Key {
     uint32_t mac_lo;  // dst MAC bytes 2..5
 };
 
+// ---------------------------------------------------------------- result words -----------
+// Every table stores the two halves of the result word it yields, ready to be written out:
+//   hi = action<<24 | next_nf<<16 | out_port ;  lo = stage<<28 | index
+SFC_HD uint32_t res_hi(uint32_t action, uint32_t nf, uint32_t port) { return (action << 24) | (nf << 16) | port; }
+SFC_HD uint32_t res_lo(uint32_t stage, uint32_t index) { return (stage << 28) | (index & 0x0FFFFFFFu); }
+constexpr uint32_t kResMissHi = (SFC_ACT_TO_CP << 24) | (SFC_NF_NONE << 16);
+constexpr uint32_t kResMissLo = 0;
+
 // ---------------------------------------------------------------- flow table -------------
-// Bucketised cuckoo table.  A slot holds the key words followed by two meta words:
-//   m0 = proto[0:8) | vlan[8:20) | action[20:22) | id[16:26) << 22
-//   m1 = out_port[0:16) | id[0:16) << 16
-// action == 3 marks an empty slot (a slot of all-ones bytes is empty).
-constexpr uint32_t kSlotEmptyWord = 0xFFFFFFFFu;
-constexpr uint32_t kFlowIdBits = 26;
-
-constexpr int kFlow4KeyWords = 3;                      // src, dst, ports
-constexpr int kFlow4SlotWords = kFlow4KeyWords + 2;    // 20 bytes
-constexpr int kFlow4BucketBytes = 32;                  // one L2 sector
-constexpr int kFlow4Slots = kFlow4BucketBytes / (4 * kFlow4SlotWords);  // 1
-constexpr int kFlow6KeyWords = 9;                      // src[4], dst[4], ports
-constexpr int kFlow6SlotWords = 12;                    // 44 bytes used, padded to 48
+// Cuckoo table, ONE slot per bucket, d = 2 or 3 bucket choices.  An IPv4 bucket is exactly one
+// 32-byte sector (one LDG.256, one L2/DRAM sector per probe); an IPv6 bucket is 64 bytes.
+//   v4 bucket words: [sip, dip, ports, tag, res_hi, res_lo, 0, 0]
+//   v6 bucket words: [sip0..3, dip0..3, ports, tag, res_hi, res_lo, 0, 0, 0, 0]
+// tag = proto | vlan<<8 | 0x80000000 (the top bit marks an occupied slot; empty slots are zero).
+constexpr uint32_t kSlotValid = 0x80000000u;
+constexpr int kFlow4BucketWords = 8;
+constexpr int kFlow6BucketWords = 16;
+constexpr int kFlow4BucketBytes = 32;
 constexpr int kFlow6BucketBytes = 64;
-constexpr int kFlow6Slots = 1;
 constexpr int kMaxHashes = 3;
+constexpr int kFlow4SeedWords = 10;  // 4 for the fold, 2 per bucket choice
+constexpr int kFlow6SeedWords = 16;  // 10 for the fold, 2 per bucket choice
 
-SFC_HD uint32_t slot_m0(uint32_t meta20, uint32_t action, uint32_t id) {
-    return (meta20 & 0xFFFFFu) | ((action & 3u) << 20) | ((id >> 16) << 22);
-}
-SFC_HD uint32_t slot_m1(uint32_t out_port, uint32_t id) { return (out_port & 0xFFFFu) | (id << 16); }
-SFC_HD uint32_t slot_action(uint32_t m0) { return (m0 >> 20) & 3u; }
-SFC_HD uint32_t slot_id(uint32_t m0, uint32_t m1) { return ((m0 >> 22) << 16) | (m1 >> 16); }
-SFC_HD uint32_t slot_port(uint32_t m1) { return m1 & 0xFFFFu; }
+// Hashing is built from 32x32->64 multiplies folded by XOR (one IMAD.WIDE + one LOP3 each on the
+// GPU).  Table correctness never depends on hash quality — every probe compares the full key —
+// only build convergence and probe counts do; the builder re-seeds if an insertion walk fails.
+SFC_HD uint64_t mul_wide(uint32_t a, uint32_t b) { return (uint64_t)a * b; }
 
-// 64-bit digest of a flow key; the d bucket choices are derived from it.
-SFC_HD uint64_t flow4_digest(uint32_t sip, uint32_t dip, uint32_t ports, uint32_t meta20,
-                             uint64_t seed) {
-    uint64_t k0 = ((uint64_t)sip << 32) | dip;
-    uint64_t k1 = ((uint64_t)ports << 32) | (meta20 & 0xFFFFFu);
-    return mix64(mix64(k0 ^ seed) + k1);
+// two 32-bit hashes (+ a third on demand) of an IPv4 5-tuple; S = kFlow4SeedWords seed words
+SFC_HD void flow4_hash(uint32_t sip, uint32_t dip, uint32_t ports, uint32_t meta20, const uint32_t* S,
+                       uint32_t& x, uint32_t& y) {
+    uint64_t P = mul_wide(sip ^ S[0], dip ^ S[1]);
+    uint64_t Q = mul_wide(ports ^ S[2], meta20 ^ S[3]);
+    x = (uint32_t)P ^ (uint32_t)(Q >> 32);
+    y = (uint32_t)(P >> 32) ^ (uint32_t)Q;
 }
-SFC_HD uint64_t flow6_digest(const uint32_t* sip, const uint32_t* dip, uint32_t ports,
-                             uint32_t meta20, uint64_t seed) {
-    uint64_t h = seed;
-    h = mix64(h ^ (((uint64_t)sip[0] << 32) | sip[1]));
-    h = mix64(h + (((uint64_t)sip[2] << 32) | sip[3]));
-    h = mix64(h ^ (((uint64_t)dip[0] << 32) | dip[1]));
-    h = mix64(h + (((uint64_t)dip[2] << 32) | dip[3]));
-    h = mix64(h ^ (((uint64_t)ports << 32) | (meta20 & 0xFFFFFu)));
-    return h;
+SFC_HD void flow6_hash(const uint32_t* sip, const uint32_t* dip, uint32_t ports, uint32_t meta20, const uint32_t* S,
+                       uint32_t& x, uint32_t& y) {
+    uint64_t P1 = mul_wide(sip[0] ^ S[0], sip[1] ^ S[1]);
+    uint64_t P2 = mul_wide(sip[2] ^ S[2], sip[3] ^ S[3]);
+    uint64_t P3 = mul_wide(dip[0] ^ S[4], dip[1] ^ S[5]);
+    uint64_t P4 = mul_wide(dip[2] ^ S[6], dip[3] ^ S[7]);
+    uint64_t Q = mul_wide(ports ^ S[8], meta20 ^ S[9]);
+    x = (uint32_t)P1 ^ (uint32_t)(P2 >> 32) ^ (uint32_t)P3 ^ (uint32_t)(P4 >> 32) ^ (uint32_t)(Q >> 32);
+    y = (uint32_t)(P1 >> 32) ^ (uint32_t)P2 ^ (uint32_t)(P3 >> 32) ^ (uint32_t)P4 ^ (uint32_t)Q;
 }
-// j-th bucket choice (j < kMaxHashes) out of nbuckets
-SFC_HD uint32_t flow_bucket(uint64_t digest, int j, uint32_t nbuckets) {
-    uint32_t h;
-    if (j == 0)
-        h = (uint32_t)digest;
-    else if (j == 1)
-        h = (uint32_t)(digest >> 32);
-    else
-        h = (uint32_t)(mix64(digest ^ 0xA5A5A5A5A5A5A5A5ull) >> 16);
-    return mulhi32(h, nbuckets);
+// j-th bucket choice from the folded pair (x, y); T = 6 seed words (two per choice)
+SFC_HD uint32_t flow_bucket(uint32_t x, uint32_t y, int j, const uint32_t* T, uint32_t nbuckets) {
+    uint64_t F = mul_wide(x ^ T[2 * j], y ^ T[2 * j + 1]);
+    return mulhi32((uint32_t)F ^ (uint32_t)(F >> 32), nbuckets);
+}
+// expands a 64-bit seed into n odd-ish 32-bit seed words
+SFC_HD void expand_seed(uint64_t seed, uint32_t* out, int n) {
+    for (int i = 0; i < n; ++i) out[i] = (uint32_t)(draw(seed, (uint64_t)i) >> 16) | 1u;
 }
 
 // ---------------------------------------------------------------- L2 steering ------------
-// exact table: open addressing, linear probing, 16-byte entries
+// exact table: open addressing, linear probing, 16-byte entries; res_hi == 0 marks an empty entry
 struct L2Entry {
     uint32_t key_lo;  // MAC bytes 2..5
     uint32_t key_hi;  // in_port << 16 | MAC bytes 0..1
-    uint32_t rule_id;
-    uint32_t val;  // bit31 valid | out_port
+    uint32_t res_lo;
+    uint32_t res_hi;
 };
 SFC_HD uint32_t l2_hash(uint32_t key_hi, uint32_t key_lo) {
-    return (uint32_t)(mix64(((uint64_t)key_hi << 32) | key_lo) >> 32);
+    uint64_t P = mul_wide(key_hi ^ 0x9E3779B1u, key_lo ^ 0x85EBCA6Bu);
+    return (uint32_t)P ^ (uint32_t)(P >> 32);
 }
-// wildcard table: indexed by in_port; {val, rule_id}, val bit31 = valid | out_port
+// wildcard table: indexed by in_port; res_hi == 0 marks "no rule"
 struct L2Wild {
-    uint32_t val;
-    uint32_t rule_id;
+    uint32_t res_hi;
+    uint32_t res_lo;
+};
+// LPM next hops: indexed by prefix id
+struct LpmRes {
+    uint32_t res_hi;
+    uint32_t res_lo;
 };
 
 // ---------------------------------------------------------------- LPM --------------------
@@ -128,7 +137,7 @@ constexpr int kAclMaxPos = 44;
 
 // ---------------------------------------------------------------- image ------------------
 constexpr uint64_t kImageMagic = 0x3130434653303042ull;  // "B00SFC01"
-constexpr uint32_t kImageVersion = 3;
+constexpr uint32_t kImageVersion = 4;
 constexpr size_t kImageAlign = 256;
 
 struct ImageHeader {
@@ -140,18 +149,16 @@ struct ImageHeader {
 
     uint64_t flow4_off;
     uint64_t flow4_seed;
-    uint32_t flow4_nbuckets, flow4_nhash, flow4_count, flow4_pad;
+    uint32_t flow4_nbuckets, flow4_nhash, flow4_count, flow4_first;  // first: slots found by probe 0
 
     uint64_t flow6_off;
     uint64_t flow6_seed;
-    uint32_t flow6_nbuckets, flow6_nhash, flow6_count, flow6_pad;
+    uint32_t flow6_nbuckets, flow6_nhash, flow6_count, flow6_first;
 
     uint64_t l2x_off;
     uint32_t l2x_mask, l2x_count;
     uint64_t l2w_off;
     uint32_t l2w_n, l2w_count;
-    uint64_t nf_off;
-    uint32_t nf_n, nf_count;
 
     uint64_t lpm4_root_off, lpm4_nodes_off, lpm4_nh_off;
     uint32_t lpm4_nnodes, lpm4_count;

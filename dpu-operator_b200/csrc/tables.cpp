@@ -134,93 +134,123 @@ struct Blob {
 };
 
 // ---- cuckoo ------------------------------------------------------------------------------
-template <int KEYW, int SLOTW, int BUCKET_BYTES, int SLOTS>
+// One slot per bucket; V6 selects the 16-word bucket / IPv6 hash.
+template <bool V6>
 struct Cuckoo {
-    static constexpr int BW = BUCKET_BYTES / 4;
+    static constexpr int BW = V6 ? kFlow6BucketWords : kFlow4BucketWords;
+    static constexpr int TAG = V6 ? 9 : 3;  // word index of the tag
     uint32_t* tab;
     uint32_t nbuckets;
     int nhash;
-    uint64_t seed;
+    uint32_t S[16];
     uint64_t rng = 0x1234567ull;
 
-    static uint64_t digest(const uint32_t* s, uint64_t seed) {
-        if (KEYW == kFlow4KeyWords) return flow4_digest(s[0], s[1], s[2], s[KEYW] & 0xFFFFFu, seed);
-        return flow6_digest(s, s + 4, s[8], s[KEYW] & 0xFFFFFu, seed);
+    void buckets(const uint32_t* rec, uint32_t* b) const {
+        uint32_t x, y;
+        if (V6) {
+            flow6_hash(rec, rec + 4, rec[8], rec[9] & 0xFFFFFu, S, x, y);
+            for (int j = 0; j < nhash; ++j) b[j] = flow_bucket(x, y, j, S + 10, nbuckets);
+        } else {
+            flow4_hash(rec[0], rec[1], rec[2], rec[3] & 0xFFFFFu, S, x, y);
+            for (int j = 0; j < nhash; ++j) b[j] = flow_bucket(x, y, j, S + 4, nbuckets);
+        }
     }
-    uint32_t* slot(uint32_t b, int s) { return tab + (size_t)b * BW + s * SLOTW; }
-    static bool empty(const uint32_t* s) { return slot_action(s[KEYW]) == 3u; }
-
     bool insert(const uint32_t* rec) {
-        uint32_t cur[SLOTW], tmp[SLOTW];
+        uint32_t cur[BW], tmp[BW];
         memcpy(cur, rec, sizeof(cur));
         uint32_t came_from = 0xFFFFFFFFu;
-        for (int kick = 0; kick < 2000; ++kick) {
-            uint64_t d = digest(cur, seed);
+        for (int kick = 0; kick < 4000; ++kick) {
             uint32_t b[kMaxHashes];
+            buckets(cur, b);
             for (int j = 0; j < nhash; ++j) {
-                b[j] = flow_bucket(d, j, nbuckets);
-                for (int s = 0; s < SLOTS; ++s) {
-                    uint32_t* p = slot(b[j], s);
-                    if (empty(p)) {
-                        memcpy(p, cur, 4 * SLOTW);
-                        return true;
-                    }
+                uint32_t* p = tab + (size_t)b[j] * BW;
+                if (!(p[TAG] & kSlotValid)) {
+                    memcpy(p, cur, 4 * BW);
+                    return true;
                 }
             }
             rng = mix64(rng + kGamma);
             int j = (int)(rng % (uint64_t)nhash);
             if (b[j] == came_from) j = (j + 1) % nhash;
-            int s = (int)((rng >> 32) % SLOTS);
-            uint32_t* p = slot(b[j], s);
-            memcpy(tmp, p, 4 * SLOTW);
-            memcpy(p, cur, 4 * SLOTW);
-            memcpy(cur, tmp, 4 * SLOTW);
+            uint32_t* p = tab + (size_t)b[j] * BW;
+            memcpy(tmp, p, 4 * BW);
+            memcpy(p, cur, 4 * BW);
+            memcpy(cur, tmp, 4 * BW);
             came_from = b[j];
         }
         return false;
     }
+    // how many occupied slots sit in their first-choice bucket (reported, and used by tests)
+    uint32_t count_first() const {
+        uint32_t n = 0, b[kMaxHashes];
+        for (uint32_t i = 0; i < nbuckets; ++i) {
+            const uint32_t* p = tab + (size_t)i * BW;
+            if (!(p[TAG] & kSlotValid)) continue;
+            buckets(p, b);
+            n += b[0] == i;
+        }
+        return n;
+    }
 };
 
-template <int KEYW, int SLOTW, int BUCKET_BYTES, int SLOTS>
-bool build_cuckoo(Blob& blob, const std::vector<const FlowRec*>& recs, int load_pct, int nhash,
-                  uint64_t& off, uint32_t& nbuckets, uint64_t& seed_out, std::string& err) {
+uint8_t nf_of_port(const RuleStore& rs, uint32_t port) {
+    for (size_t i = 0; i < rs.nf_in.size(); ++i)
+        if (rs.nf_in[i] == port || rs.nf_out[i] == port) return (uint8_t)i;  // lowest NF index wins
+    return (uint8_t)SFC_NF_NONE;
+}
+
+template <bool V6>
+bool build_cuckoo(Blob& blob, const RuleStore& rs, const std::vector<const FlowRec*>& recs, uint64_t& off,
+                  uint32_t& nbuckets, uint64_t& seed_out, uint32_t& first_out, std::string& err) {
+    constexpr int BW = Cuckoo<V6>::BW;
     size_t n = recs.size();
-    int max_load = (SLOTS == 1) ? (nhash == 2 ? 45 : 85) : 90;
-    load_pct = std::min(std::max(load_pct, 5), max_load);
-    uint64_t nb = std::max<uint64_t>(8, (n * 100 + (uint64_t)load_pct * SLOTS - 1) / ((uint64_t)load_pct * SLOTS));
+    int nhash = rs.flow_hashes;
+    int max_load = nhash == 2 ? 45 : 85;
+    int load_pct = std::min(std::max(rs.flow_load_pct, 5), max_load);
+    uint64_t nb = std::max<uint64_t>(8, (n * 100 + (uint64_t)load_pct - 1) / (uint64_t)load_pct);
+    // precompute next_nf per port once
+    std::vector<uint8_t> nf(SFC_MAX_PORTS, (uint8_t)SFC_NF_NONE);
+    for (uint32_t p = 0; p < SFC_MAX_PORTS; ++p) nf[p] = nf_of_port(rs, p);
     for (int grow = 0; grow < 6; ++grow, nb = nb + nb / 8 + 1) {
         if (nb > 0xFFFFFFF0ull) break;
         for (int attempt = 0; attempt < 4; ++attempt) {
             size_t start = blob.img.size();
-            off = blob.reserve((size_t)nb * BUCKET_BYTES, 0xFF);
-            Cuckoo<KEYW, SLOTW, BUCKET_BYTES, SLOTS> c;
+            off = blob.reserve((size_t)nb * BW * 4, 0x00);
+            Cuckoo<V6> c;
             c.tab = blob.at<uint32_t>(off);
             c.nbuckets = (uint32_t)nb;
             c.nhash = nhash;
-            c.seed = mix64(0x5FC0C0DEull + 977ull * attempt + 31ull * grow);
+            uint64_t seed = mix64(0x5FC0C0DEull + 977ull * attempt + 31ull * grow + (V6 ? 7ull : 0ull));
+            expand_seed(seed, c.S, V6 ? kFlow6SeedWords : kFlow4SeedWords);
             bool ok = true;
-            uint32_t rec[SLOTW];
+            uint32_t rec[BW];
             for (size_t i = 0; i < n && ok; ++i) {
                 const FlowRec& f = *recs[i];
-                for (int w = 0; w < SLOTW; ++w) rec[w] = 0;
-                if (KEYW == kFlow4KeyWords) {
+                for (int w = 0; w < BW; ++w) rec[w] = 0;
+                int t;
+                if (!V6) {
                     rec[0] = f.sip[0];
                     rec[1] = f.dip[0];
                     rec[2] = f.ports;
+                    t = 3;
                 } else {
                     for (int w = 0; w < 4; ++w) {
                         rec[w] = f.sip[w];
                         rec[4 + w] = f.dip[w];
                     }
                     rec[8] = f.ports;
+                    t = 9;
                 }
-                rec[KEYW] = slot_m0(f.meta, f.action, f.id);
-                rec[KEYW + 1] = slot_m1(f.out_port, f.id);
+                rec[t] = (f.meta & 0xFFFFFu) | kSlotValid;
+                uint32_t nfv = f.action == SFC_ACT_FORWARD ? nf[f.out_port] : (uint32_t)SFC_NF_NONE;
+                rec[t + 1] = res_hi(f.action, nfv, f.out_port);
+                rec[t + 2] = res_lo(SFC_STAGE_FLOW, f.id);
                 ok = c.insert(rec);
             }
             if (ok) {
                 nbuckets = (uint32_t)nb;
-                seed_out = c.seed;
+                seed_out = seed;
+                first_out = c.count_first();
                 return true;
             }
             blob.img.resize(start);
@@ -282,7 +312,7 @@ struct Trie {
     }
 };
 
-void build_lpm(Blob& blob, const std::map<RuleStore::LpmKey, LpmRec>& recs_map, uint64_t& root_off, uint64_t& nodes_off,
+void build_lpm(Blob& blob, const RuleStore& rs, int af, const std::map<RuleStore::LpmKey, LpmRec>& recs_map, uint64_t& root_off, uint64_t& nodes_off,
                uint64_t& nh_off, uint32_t& nnodes, uint32_t& count) {
     std::vector<const LpmRec*> sorted;
     std::vector<LpmRec> recs;
@@ -305,8 +335,12 @@ void build_lpm(Blob& blob, const std::map<RuleStore::LpmKey, LpmRec>& recs_map, 
     nodes_off = blob.reserve(std::max<size_t>(t.nodes.size() * 4, 4), 0);
     if (!t.nodes.empty()) memcpy(blob.at<uint8_t>(nodes_off), t.nodes.data(), t.nodes.size() * 4);
     size_t nh_n = recs.empty() ? 1 : (size_t)max_id + 1;
-    nh_off = blob.reserve(nh_n * 2, 0);
-    for (auto& r : recs) blob.at<uint16_t>(nh_off)[r.id] = r.out_port;
+    nh_off = blob.reserve(nh_n * sizeof(LpmRes), 0);
+    for (auto& r : recs) {
+        LpmRes& e = blob.at<LpmRes>(nh_off)[r.id];
+        e.res_hi = res_hi(SFC_ACT_FORWARD, nf_of_port(rs, r.out_port), r.out_port);
+        e.res_lo = res_lo(af == 4 ? SFC_STAGE_LPM4 : SFC_STAGE_LPM6, r.id);
+    }
 }
 
 // ---- ACL ---------------------------------------------------------------------------------
@@ -443,12 +477,8 @@ bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& imag
     H.flow4_count = (uint32_t)f4.size();
     H.flow6_count = (uint32_t)f6.size();
     H.flow4_nhash = H.flow6_nhash = (uint32_t)rs.flow_hashes;
-    if (!build_cuckoo<kFlow4KeyWords, kFlow4SlotWords, kFlow4BucketBytes, kFlow4Slots>(
-            blob, f4, rs.flow_load_pct, rs.flow_hashes, H.flow4_off, H.flow4_nbuckets, H.flow4_seed, err))
-        return false;
-    if (!build_cuckoo<kFlow6KeyWords, kFlow6SlotWords, kFlow6BucketBytes, kFlow6Slots>(
-            blob, f6, rs.flow_load_pct, rs.flow_hashes, H.flow6_off, H.flow6_nbuckets, H.flow6_seed, err))
-        return false;
+    if (!build_cuckoo<false>(blob, rs, f4, H.flow4_off, H.flow4_nbuckets, H.flow4_seed, H.flow4_first, err)) return false;
+    if (!build_cuckoo<true>(blob, rs, f6, H.flow6_off, H.flow6_nbuckets, H.flow6_seed, H.flow6_first, err)) return false;
 
     // L2 steering: resolve OpenFlow priorities per match, exact and wildcard apart
     {
@@ -479,37 +509,23 @@ bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& imag
         for (auto& kv : exact) {
             L2Entry* tab = blob.at<L2Entry>(H.l2x_off);
             uint32_t i = l2_hash(kv.first.first, kv.first.second) & H.l2x_mask;
-            while (tab[i].val & 0x80000000u) i = (i + 1) & H.l2x_mask;
+            while (tab[i].res_hi) i = (i + 1) & H.l2x_mask;
             tab[i].key_hi = kv.first.first;
             tab[i].key_lo = kv.first.second;
-            tab[i].rule_id = kv.second->id;
-            tab[i].val = 0x80000000u | kv.second->out_port;
+            tab[i].res_lo = res_lo(SFC_STAGE_L2_EXACT, kv.second->id);
+            tab[i].res_hi = res_hi(SFC_ACT_FORWARD, nf_of_port(rs, kv.second->out_port), kv.second->out_port);
         }
         H.l2w_n = rs.l2.empty() ? 1 : max_port + 1;
         H.l2w_count = (uint32_t)wild.size();
         H.l2w_off = blob.reserve((size_t)H.l2w_n * sizeof(L2Wild), 0);
         for (auto& kv : wild) {
             L2Wild* w = blob.at<L2Wild>(H.l2w_off);
-            w[kv.first].val = 0x80000000u | kv.second->out_port;
-            w[kv.first].rule_id = kv.second->id;
+            w[kv.first].res_hi = res_hi(SFC_ACT_FORWARD, nf_of_port(rs, kv.second->out_port), kv.second->out_port);
+            w[kv.first].res_lo = res_lo(SFC_STAGE_L2_WILD, kv.second->id);
         }
     }
-    // NF ownership of ports
-    {
-        uint32_t max_port = 0;
-        for (auto p : rs.nf_in) max_port = std::max<uint32_t>(max_port, p);
-        for (auto p : rs.nf_out) max_port = std::max<uint32_t>(max_port, p);
-        H.nf_n = max_port + 1;
-        H.nf_count = (uint32_t)rs.nf_in.size();
-        H.nf_off = blob.reserve(H.nf_n, (uint8_t)SFC_NF_NONE);
-        // first declaration wins if a port is named twice (lowest NF index)
-        for (size_t i = rs.nf_in.size(); i-- > 0;) {
-            blob.at<uint8_t>(H.nf_off)[rs.nf_out[i]] = (uint8_t)i;
-            blob.at<uint8_t>(H.nf_off)[rs.nf_in[i]] = (uint8_t)i;
-        }
-    }
-    build_lpm(blob, rs.lpm4, H.lpm4_root_off, H.lpm4_nodes_off, H.lpm4_nh_off, H.lpm4_nnodes, H.lpm4_count);
-    build_lpm(blob, rs.lpm6, H.lpm6_root_off, H.lpm6_nodes_off, H.lpm6_nh_off, H.lpm6_nnodes, H.lpm6_count);
+    build_lpm(blob, rs, 4, rs.lpm4, H.lpm4_root_off, H.lpm4_nodes_off, H.lpm4_nh_off, H.lpm4_nnodes, H.lpm4_count);
+    build_lpm(blob, rs, 6, rs.lpm6, H.lpm6_root_off, H.lpm6_nodes_off, H.lpm6_nh_off, H.lpm6_nnodes, H.lpm6_count);
     build_acl(blob, rs.acl, H);
 
     size_t total = (image.size() + kImageAlign - 1) / kImageAlign * kImageAlign;
@@ -539,10 +555,10 @@ bool validate_image(const uint8_t* img, size_t len, std::string& err) {
               inside(H.flow6_off, (uint64_t)H.flow6_nbuckets * kFlow6BucketBytes) &&
               inside(H.l2x_off, ((uint64_t)H.l2x_mask + 1) * sizeof(L2Entry)) &&
               ((H.l2x_mask & (H.l2x_mask + 1)) == 0) && inside(H.l2w_off, (uint64_t)H.l2w_n * sizeof(L2Wild)) &&
-              inside(H.nf_off, H.nf_n) && inside(H.lpm4_root_off, 65536 * 4) &&
+              inside(H.lpm4_root_off, 65536 * 4) &&
               inside(H.lpm4_nodes_off, (uint64_t)H.lpm4_nnodes * 1024) && inside(H.lpm6_root_off, 65536 * 4) &&
-              inside(H.lpm6_nodes_off, (uint64_t)H.lpm6_nnodes * 1024) && inside(H.lpm4_nh_off, 2) &&
-              inside(H.lpm6_nh_off, 2) && H.flow4_nhash >= 1 && H.flow4_nhash <= kMaxHashes &&
+              inside(H.lpm6_nodes_off, (uint64_t)H.lpm6_nnodes * 1024) && inside(H.lpm4_nh_off, 8) &&
+              inside(H.lpm6_nh_off, 8) && H.flow4_nhash >= 1 && H.flow4_nhash <= kMaxHashes &&
               H.flow6_nhash >= 1 && H.flow6_nhash <= kMaxHashes && H.flow4_nbuckets && H.flow6_nbuckets &&
               H.acl_npos4 <= kAclMaxPos && H.acl_npos6 <= kAclMaxPos && H.acl_nrules <= SFC_MAX_ACL_RULES;
     if (ok && H.acl_nrules)

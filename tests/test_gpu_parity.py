@@ -255,3 +255,35 @@ def test_flow_roundtrip_property_16m(torch_cuda):
         assert (p["ver"], p["vlan"], p["proto"], p["sport"], p["dport"]) == (k["ip_ver"], k["vlan"], k["proto"], k["sport"], k["dport"])
         assert p["src"][:w] == bytes(k["src"][:w]) and p["dst"][:w] == bytes(k["dst"][:w])
         assert act[i] == acts[0]["action"] and port[i] == acts[0]["out_port"]
+
+
+def test_repeated_launches_are_stable(torch_cuda):
+    """Race guard.  An early version released a shared-memory tile to the TMA producer before the
+    consumers' LDS data had actually returned; it showed up as a few wrong rows once in hundreds of
+    launches.  Hammer the kernel with back-to-back launches over rotating batches and demand
+    bit-exact results every time."""
+    torch = torch_cuda
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    spec = config2_spec()
+    install_flows(sc, spec)
+    dp.commit()
+    pool, n = 4, 1 << 20
+    hdr = torch.empty((pool, n, 64), dtype=torch.uint8, device="cuda")
+    ports = torch.empty((pool, n), dtype=torch.int16, device="cuda")
+    res = torch.zeros((pool, n), dtype=torch.int64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    for b in range(pool):
+        dp.gen_packets(spec, b * n, n, hdr[b].data_ptr(), ports[b].data_ptr(), st)
+    torch.cuda.synchronize()
+    want = torch.stack([
+        torch.from_numpy(sc.orc.classify(hdr[b].cpu().numpy(), ports[b].cpu().numpy().view(np.uint16), threads=8).view(np.int64))
+        for b in range(pool)]).cuda()
+    for it in range(25):
+        res.zero_()
+        for i in range(pool * 8):
+            b = i % pool
+            dp.classify(hdr[b].data_ptr(), ports[b].data_ptr(), res[b].data_ptr(), n, 0, st)
+        torch.cuda.synchronize()
+        bad = int((res != want).sum().item())
+        assert bad == 0, f"iteration {it}: {bad} results differ from the oracle"
