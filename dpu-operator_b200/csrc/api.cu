@@ -21,8 +21,9 @@
 using namespace sfc;
 
 namespace {
-constexpr int kTile = 128;
-constexpr int kStages = 4;
+constexpr int kTile = 256;
+constexpr int kStages = 2;
+constexpr int kTicketRing = 32;      // a launch uses slot seq % 32 and clears slot (seq + 16) % 32
 constexpr size_t kHostChunk = 1u << 18;  // packets per pipelined chunk in sfc_classify_host
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -46,6 +47,7 @@ struct sfc_handle {
     int ctas_per_sm[16] = {0};
     int tune_tile = 0, tune_stages = 0;  // SFC_TUNE=tile,stages (experiments)
     uint32_t flow_first[2] = {0, 0};
+    uint32_t* d_tickets = nullptr;  // ring of kTicketRing tile-ticket counters (scratch of the classify kernel)
     // sfc_classify_host staging
     cudaStream_t hs[2] = {nullptr, nullptr};
     cudaEvent_t ev[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
@@ -152,7 +154,7 @@ int install_image_from_host(sfc_handle* h, const uint8_t* img, size_t len) {
 
 template <int TILE, int STAGES, bool C, bool A>
 int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
-                   cudaStream_t st) {
+                   uint32_t flags, cudaStream_t st) {
     auto kern = classify_kernel<TILE, STAGES, C, A>;
     constexpr int smem = SmemLayout<TILE, STAGES, A>::kBytes;
     if (!h->ctas_per_sm[slot]) {
@@ -173,8 +175,21 @@ int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_
     if (r != CUDA_SUCCESS) return fail(h, -EIO, "cuTensorMapEncodeTiled failed (%d)", (int)r);
     uint64_t n_tiles = (n + TILE - 1) / TILE;
     uint64_t grid = std::min<uint64_t>(n_tiles, (uint64_t)h->sm_count * h->ctas_per_sm[slot]);
-    kern<<<(unsigned)grid, TILE + 32, smem, st>>>(map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, h->T);
-    CUDA_TRY(h, cudaGetLastError());
+    uint32_t* ticket = h->d_tickets + (h->launches % kTicketRing);
+    uint32_t* stale = h->d_tickets + ((h->launches + kTicketRing / 2) % kTicketRing);
+    uint32_t overlap = (flags & SFC_F_OVERLAP) ? 1u : 0u;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(TILE + 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = overlap ? 1 : 0;
+    CUDA_TRY(h, cudaLaunchKernelEx(&cfg, kern, map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, stale,
+                                   overlap, h->T));
     ++h->launches;
     return 0;
 }
@@ -187,7 +202,7 @@ int launch_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uin
     bool c = flags & SFC_F_COUNTERS, a = h->T.acl_nrules > 0;
     if (!c && !a && h->tune_tile) {  // experiment hook: SFC_TUNE=tile,stages
 #define SFC_TUNE_CASE(slot, T_, S_) \
-    if (h->tune_tile == T_ && h->tune_stages == S_) return launch_variant<T_, S_, false, false>(h, slot, hdr, in_port, result, n, st);
+    if (h->tune_tile == T_ && h->tune_stages == S_) return launch_variant<T_, S_, false, false>(h, slot, hdr, in_port, result, n, flags, st);
         SFC_TUNE_CASE(4, 64, 4)
         SFC_TUNE_CASE(5, 128, 2)
         SFC_TUNE_CASE(6, 128, 3)
@@ -199,10 +214,10 @@ int launch_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uin
         SFC_TUNE_CASE(12, 768, 2)
 #undef SFC_TUNE_CASE
     }
-    if (c && a) return launch_variant<kTile, kStages, true, true>(h, 3, hdr, in_port, result, n, st);
-    if (c) return launch_variant<kTile, kStages, true, false>(h, 2, hdr, in_port, result, n, st);
-    if (a) return launch_variant<kTile, kStages, false, true>(h, 1, hdr, in_port, result, n, st);
-    return launch_variant<kTile, kStages, false, false>(h, 0, hdr, in_port, result, n, st);
+    if (c && a) return launch_variant<kTile, kStages, true, true>(h, 3, hdr, in_port, result, n, flags, st);
+    if (c) return launch_variant<kTile, kStages, true, false>(h, 2, hdr, in_port, result, n, flags, st);
+    if (a) return launch_variant<kTile, kStages, false, true>(h, 1, hdr, in_port, result, n, flags, st);
+    return launch_variant<kTile, kStages, false, false>(h, 0, hdr, in_port, result, n, flags, st);
 }
 
 __global__ void gen_kernel(sfc_gen_spec spec, uint64_t first, uint64_t n, uint8_t* hdr, uint16_t* in_port) {
@@ -255,7 +270,9 @@ int sfc_create(int device_ordinal, sfc_handle** out) {
     h->encode = (EncodeTiledFn)fn;
     if (const char* tune = getenv("SFC_TUNE")) sscanf(tune, "%d,%d", &h->tune_tile, &h->tune_stages);
     if (cudaMalloc(&h->d_counters, SFC_CNT_TOTAL * sizeof(uint64_t)) != cudaSuccess ||
-        cudaMemset(h->d_counters, 0, SFC_CNT_TOTAL * sizeof(uint64_t)) != cudaSuccess) {
+        cudaMemset(h->d_counters, 0, SFC_CNT_TOTAL * sizeof(uint64_t)) != cudaSuccess ||
+        cudaMalloc(&h->d_tickets, kTicketRing * sizeof(uint32_t)) != cudaSuccess ||
+        cudaMemset(h->d_tickets, 0, kTicketRing * sizeof(uint32_t)) != cudaSuccess) {
         delete h;
         return -ENOMEM;
     }
@@ -273,6 +290,7 @@ int sfc_destroy(sfc_handle* h) {
     cudaDeviceSynchronize();
     if (h->d_image) cudaFree(h->d_image);
     if (h->d_counters) cudaFree(h->d_counters);
+    if (h->d_tickets) cudaFree(h->d_tickets);
     for (int i = 0; i < 2; ++i) {
         if (h->d_hdr[i]) cudaFree(h->d_hdr[i]);
         if (h->d_port[i]) cudaFree(h->d_port[i]);

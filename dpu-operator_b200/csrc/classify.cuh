@@ -227,14 +227,15 @@ template <int TILE, int STAGES, bool ACL>
 struct SmemLayout {
     static constexpr int kTileBytes = TILE * 64;
     static constexpr int kAclBytes = ACL ? (TILE / 32) * kAclKeyWords * 32 * 4 : 0;
-    static constexpr int kBytes = STAGES * kTileBytes + kAclBytes + 2 * STAGES * 8 + 16 * 8 + 32 * 4 + 1024;
+    static constexpr int kBytes = STAGES * kTileBytes + kAclBytes + 2 * STAGES * 8 + 16 * 8 + 32 * 4 + STAGES * 4 + 16 + 1024;
 };
 
 template <int TILE, int STAGES, bool COUNTERS, bool ACL>
 __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
                                                               const uint16_t* __restrict__ in_port,
                                                               uint64_t* __restrict__ result, uint32_t n,
-                                                              uint32_t n_tiles,
+                                                              uint32_t n_tiles, uint32_t* tile_counter,
+                                                              uint32_t* stale_counter, uint32_t overlap,
                                                               const __grid_constant__ DevTables T) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -244,6 +245,7 @@ __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_consta
     uint64_t* empty = full + STAGES;
     unsigned long long* scnt = (unsigned long long*)(empty + STAGES);  // 16 block-level counters
     uint32_t* dep_sink = (uint32_t*)(scnt + 16);                       // one word per consumer warp
+    uint32_t* tile_of = dep_sink + 32;                                 // tile index held by each stage
 
     const int tid = threadIdx.x;
     constexpr int kConsumerWarps = TILE / 32;
@@ -261,17 +263,33 @@ __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_consta
 
     if (tid >= TILE) {
         // ---------------- producer warp: one lane feeds the ring ----------------
+        // Tiles are handed out dynamically: the first one is the CTA's own index, the rest come from
+        // a global ticket counter, so SMs that run slow (far L2 die, unlucky probes) simply take
+        // fewer tiles.  The draw for the next tile is issued before waiting on the current slot.
         if (tid == TILE) {
+            if (overlap) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+            if (blockIdx.x == 0) *stale_counter = 0;  // the ticket counter of a launch 16 calls from now
             uint64_t pol = policy_evict_first();
-            uint32_t it = 0;
-            for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-                uint32_t s = it % STAGES, use = it / STAGES;
+            uint32_t tile = blockIdx.x;
+            for (uint32_t it = 0;; ++it) {
+                const uint32_t s = it % STAGES, use = it / STAGES;
+                const bool have = tile < n_tiles;
+                uint32_t next = 0;
+                if (have) next = gridDim.x + atomicAdd(tile_counter, 1u);
                 if (use > 0) mbar_wait(empty + s, (use - 1) & 1);
+                tile_of[s] = have ? tile : 0xFFFFFFFFu;
+                if (!have) {
+                    mbar_arrive(full + s);  // end marker: no bytes will follow
+                    break;
+                }
                 mbar_arrive_expect_tx(full + s, TILE * 64);
 #pragma unroll
                 for (int r = 0; r < TILE; r += kBoxRows)  // a TMA box is at most 256 rows
                     tma_load_tile(tiles + s * TILE * 64 + r * 64, &hdr_map, 0, (int)(tile * TILE) + r, full + s, pol);
+                tile = next;
             }
+            // keep stream order intact when launches overlap: do not retire before the previous grid has
+            if (overlap) asm volatile("griddepcontrol.wait;" ::: "memory");
         }
         return;
     }
@@ -279,14 +297,14 @@ __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_consta
     const int lane = tid & 31;
     const uint32_t row_off = (uint32_t)tid * 64u;
     const uint32_t sw = ((uint32_t)tid >> 1) & 3u;
-    uint32_t it = 0;
-    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+    for (uint32_t it = 0;; ++it) {
         const uint32_t s = it % STAGES, use = it / STAGES;
+        mbar_wait(full + s, use & 1);
+        const uint32_t tile = tile_of[s];
+        if (tile == 0xFFFFFFFFu) break;
         const uint32_t pkt = tile * TILE + tid;
         const bool live = pkt < n;
         const uint32_t port = live ? (uint32_t)__ldg(in_port + pkt) : 0u;
-
-        mbar_wait(full + s, use & 1);
         uint32_t w[16];
         const uint32_t base = smem_u32(tiles + s * TILE * 64) + row_off;
 #pragma unroll
@@ -303,7 +321,7 @@ __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_consta
         // B200 as sporadic wrong rows).  Folding one word of each of the four loads into a value
         // that lane 0 stores makes the store — issued in order before the arrive — wait on the
         // warp-wide scoreboard of all four LDS instructions.
-        const uint32_t dep = w[3] ^ w[7] ^ w[11] ^ w[15];
+        const uint32_t dep = w[3] ^ w[7] ^ w[11] ^ w[15] ^ tile;
         __syncwarp();
         if (lane == 0) {
             asm volatile("st.shared.u32 [%0], %1;" ::"r"(smem_u32(dep_sink + (tid >> 5))), "r"(dep) : "memory");

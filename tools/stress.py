@@ -28,7 +28,7 @@ for tile, stages in VARIANTS:
         res.zero_()
         for i in range(POOL * 4):
             b = i % POOL
-            dp.classify(hdr[b].data_ptr(), ports[b].data_ptr(), res[b].data_ptr(), BATCH, 0, st)
+            dp.classify(hdr[b].data_ptr(), ports[b].data_ptr(), res[b].data_ptr(), BATCH, int(os.environ.get("SFC_FLAGS", "0")), st)
         torch.cuda.synchronize()
         bad = (res != want).nonzero()
         if bad.numel():

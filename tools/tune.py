@@ -36,6 +36,7 @@ def setup(mode):
     return dp, spec
 
 
+FLAGS = int(os.environ.get("SFC_FLAGS", "0"))
 for mode in sys.argv[1:] or ["empty", "cfg2"]:
     dp, spec = setup(mode)
     st = torch.cuda.current_stream().cuda_stream
@@ -51,7 +52,7 @@ for mode in sys.argv[1:] or ["empty", "cfg2"]:
         def run(k):
             for i in range(k):
                 b = i % POOL
-                dp.classify(hdr[b].data_ptr(), ports[b].data_ptr(), res[b].data_ptr(), BATCH, 0, st)
+                dp.classify(hdr[b].data_ptr(), ports[b].data_ptr(), res[b].data_ptr(), BATCH, FLAGS, st)
         run(300); torch.cuda.synchronize()
         best = 1e9
         for rep in range(3):
