@@ -21,7 +21,7 @@
 using namespace sfc;
 
 namespace {
-constexpr int kTile = 256;
+constexpr int kTile = 128;
 constexpr int kStages = 2;
 constexpr int kTicketRing = 32;      // a launch uses slot seq % 32 and clears slot (seq + 16) % 32
 constexpr size_t kHostChunk = 1u << 18;  // packets per pipelined chunk in sfc_classify_host
@@ -47,6 +47,7 @@ struct sfc_handle {
     int ctas_per_sm[16] = {0};
     int tune_tile = 0, tune_stages = 0;  // SFC_TUNE=tile,stages (experiments)
     uint32_t flow_first[2] = {0, 0};
+    int probe_mode = -1;  // option "flow_probe_mode": -1 auto, else kProbe* bits
     uint32_t* d_tickets = nullptr;  // ring of kTicketRing tile-ticket counters (scratch of the classify kernel)
     // sfc_classify_host staging
     cudaStream_t hs[2] = {nullptr, nullptr};
@@ -102,6 +103,14 @@ void bind_tables(sfc_handle* h) {
     T.flow4_nbuckets = H.flow4_nbuckets;
     T.flow4_nhash = H.flow4_nhash;
     T.flow4_count = H.flow4_count;
+    {   // probe strategy by where the table will live.  Measured on B200 (tools/tune.py): a table of
+        // <= 128 KB stays in L1 and both probes at once win (14.8 vs 15.8 us per 1M packets); for
+        // anything larger the second load only adds L2/DRAM sectors (eager is 8-40% slower).
+        uint64_t bytes = (uint64_t)H.flow4_nbuckets * kFlow4BucketBytes;
+        uint32_t mode = bytes <= (128u << 10) ? (kProbeEager | kProbeL1) : 0u;
+        if (h->probe_mode >= 0) mode = (uint32_t)h->probe_mode;
+        T.flow4_mode = mode;
+    }
     T.flow6_nbuckets = H.flow6_nbuckets;
     T.flow6_nhash = H.flow6_nhash;
     T.flow6_count = H.flow6_count;
@@ -315,6 +324,12 @@ int sfc_set_option(sfc_handle* h, const char* name, long value) {
     if (!strcmp(name, "flow_hashes")) {
         if (value < 2 || value > kMaxHashes) return fail(h, -EINVAL, "flow_hashes must be 2 or 3");
         h->rs.flow_hashes = (int)value;
+        return 0;
+    }
+    if (!strcmp(name, "flow_probe_mode")) {  // -1 auto, bit0 eager dual probe, bit1 probes may live in L1
+        if (value < -1 || value > 3) return fail(h, -EINVAL, "flow_probe_mode must be -1..3");
+        h->probe_mode = (int)value;
+        if (h->d_image) h->T.flow4_mode = value >= 0 ? (uint32_t)value : h->T.flow4_mode;
         return 0;
     }
     if (!strcmp(name, "tune_tile")) {  // experiment hooks: pick a compiled (tile, stages) variant

@@ -16,10 +16,13 @@
 
 namespace sfc {
 
+constexpr uint32_t kProbeEager = 1u, kProbeL1 = 2u;
+
 struct DevTables {
     const uint32_t* flow4;
     const uint32_t* flow6;
     uint32_t flow4_nbuckets, flow4_nhash, flow4_count;
+    uint32_t flow4_mode;  // kProbeEager: issue both probes at once; kProbeL1: let probes allocate in L1
     uint32_t flow6_nbuckets, flow6_nhash, flow6_count;
     uint32_t S4[kFlow4SeedWords];
     uint32_t S6[kFlow6SeedWords];
@@ -87,6 +90,12 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 // one 32-byte sector, read-only path
 __device__ __forceinline__ void ldg256(const void* p, uint32_t* r) {
     asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "l"(p));
+}
+// same sector, allowed to stay in L1 (tables small enough to live there)
+__device__ __forceinline__ void ldg256_l1(const void* p, uint32_t* r) {
+    asm volatile("ld.global.nc.L1::evict_last.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "l"(p));
 }
@@ -161,25 +170,47 @@ __device__ __forceinline__ bool parse_header(uint32_t* w, Key& k) {
 }
 
 // ------------------------------------------------------------------ stage 2: flows -------
-// One 32-byte sector per probe; the first-choice bucket holds most flows (the builder reports how
-// many), so the second load is predicated on a miss instead of being issued up front.
+// One 32-byte sector per probe.  Two strategies, picked per table by the host (flow4_mode):
+//  - lazy  (tables that live in HBM): probe the first-choice bucket, which holds most flows (the
+//    builder reports how many), and load the second only on a miss — fewest DRAM sectors;
+//  - eager (tables that fit L2/L1): issue both loads at once — one latency instead of two.
+__device__ __forceinline__ bool flow4_match(const uint32_t* s, const Key& k, uint32_t tag) {
+    return s[0] == k.sip[0] && s[1] == k.dip[0] && s[2] == k.ports && s[3] == tag;
+}
 __device__ __forceinline__ bool flow4_lookup(const DevTables& T, const Key& k, uint32_t& rhi, uint32_t& rlo) {
     const uint32_t meta20 = k.meta & 0xFFFFFu, tag = meta20 | kSlotValid;
     uint32_t x, y;
     flow4_hash(k.sip[0], k.dip[0], k.ports, meta20, T.S4, x, y);
-    const uint32_t b0 = flow_bucket(x, y, 0, T.S4 + 4, T.flow4_nbuckets);
-    const uint32_t b1 = flow_bucket(x, y, 1, T.S4 + 4, T.flow4_nbuckets);
-    uint32_t s[8];
-    ldg256(T.flow4 + (size_t)b0 * kFlow4BucketWords, s);
-    bool hit = s[0] == k.sip[0] && s[1] == k.dip[0] && s[2] == k.ports && s[3] == tag;
-    if (!hit) {
-        ldg256(T.flow4 + (size_t)b1 * kFlow4BucketWords, s);
-        hit = s[0] == k.sip[0] && s[1] == k.dip[0] && s[2] == k.ports && s[3] == tag;
-        if (!hit && T.flow4_nhash > 2) {
-            const uint32_t b2 = flow_bucket(x, y, 2, T.S4 + 4, T.flow4_nbuckets);
-            ldg256(T.flow4 + (size_t)b2 * kFlow4BucketWords, s);
-            hit = s[0] == k.sip[0] && s[1] == k.dip[0] && s[2] == k.ports && s[3] == tag;
+    const uint32_t* p0 = T.flow4 + (size_t)flow_bucket(x, y, 0, T.S4 + 4, T.flow4_nbuckets) * kFlow4BucketWords;
+    const uint32_t* p1 = T.flow4 + (size_t)flow_bucket(x, y, 1, T.S4 + 4, T.flow4_nbuckets) * kFlow4BucketWords;
+    uint32_t s[8], t[8];
+    bool hit;
+    if (T.flow4_mode & kProbeEager) {
+        if (T.flow4_mode & kProbeL1) {
+            ldg256_l1(p0, s);
+            ldg256_l1(p1, t);
+        } else {
+            ldg256(p0, s);
+            ldg256(p1, t);
         }
+        hit = flow4_match(s, k, tag);
+        if (!hit) {
+            hit = flow4_match(t, k, tag);
+            s[4] = t[4];
+            s[5] = t[5];
+        }
+    } else {
+        ldg256(p0, s);
+        hit = flow4_match(s, k, tag);
+        if (!hit) {
+            ldg256(p1, s);
+            hit = flow4_match(s, k, tag);
+        }
+    }
+    if (!hit && T.flow4_nhash > 2) {
+        const uint32_t b2 = flow_bucket(x, y, 2, T.S4 + 4, T.flow4_nbuckets);
+        ldg256(T.flow4 + (size_t)b2 * kFlow4BucketWords, s);
+        hit = flow4_match(s, k, tag);
     }
     rhi = s[4];
     rlo = s[5];

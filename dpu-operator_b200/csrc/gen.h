@@ -201,7 +201,7 @@ SFC_HD void gen_packet(const sfc_gen_spec& s, uint64_t i, uint8_t* h, uint16_t& 
     if (f.ip_ver == 4) {
         put16(h + off, 0x0800);
         uint8_t* ip = h + off + 2;
-        uint32_t ihl = ((uint32_t)(p3 >> 56) & 0xFu) == 0 ? 6u : 5u;
+        uint32_t ihl = ((uint32_t)(p3 >> 56) & 0xFFu) == 0 ? 6u : 5u;  // 1 in 256 carries IP options
         bool frag = ((uint32_t)(p3 >> 56) & 0xFFu) == 0x11u;
         ip[0] = (uint8_t)(0x40u | ihl);
         put16(ip + 2, 46);

@@ -47,7 +47,9 @@ for mode in sys.argv[1:] or ["empty", "cfg2"]:
         dp.gen_packets(spec, b * BATCH, BATCH, hdr[b].data_ptr(), ports[b].data_ptr(), st)
     torch.cuda.synchronize()
     ref = None
-    for tile, stages in VARIANTS:
+    pm = int(os.environ.get("SFC_PROBE", "-1"))
+    dp.set_option("flow_probe_mode", pm)
+    for tile, stages in [tuple(map(int, v.split("x"))) for v in os.environ.get("SFC_VARIANTS", "0x0,128x2,128x3,256x2,256x3,512x2").split(",")]:
         dp.set_option("tune_tile", tile); dp.set_option("tune_stages", stages)
         def run(k):
             for i in range(k):
