@@ -91,11 +91,8 @@ struct DeviceGuard {
     }
 };
 
-void bind_tables(sfc_handle* h) {
-    ImageHeader H;
-    cudaMemcpy(&H, h->d_image, sizeof(H), cudaMemcpyDeviceToHost);
-    DevTables& T = h->T;
-    const uint8_t* b = h->d_image;
+// Resolve the section offsets of an image header against the device address the image sits at.
+void fill_tables(DevTables& T, const ImageHeader& H, const uint8_t* b, unsigned long long* counters, int probe_mode) {
     T.flow4 = (const uint32_t*)(b + H.flow4_off);
     T.flow6 = (const uint32_t*)(b + H.flow6_off);
     expand_seed(H.flow4_seed, T.S4, kFlow4SeedWords);
@@ -108,7 +105,7 @@ void bind_tables(sfc_handle* h) {
         // anything larger the second load only adds L2/DRAM sectors (eager is 8-40% slower).
         uint64_t bytes = (uint64_t)H.flow4_nbuckets * kFlow4BucketBytes;
         uint32_t mode = bytes <= (128u << 10) ? (kProbeEager | kProbeL1) : 0u;
-        if (h->probe_mode >= 0) mode = (uint32_t)h->probe_mode;
+        if (probe_mode >= 0) mode = (uint32_t)probe_mode;
         T.flow4_mode = mode;
     }
     T.flow6_nbuckets = H.flow6_nbuckets;
@@ -139,7 +136,13 @@ void bind_tables(sfc_handle* h) {
     memcpy(T.acl_pos6, H.acl_pos6, kAclMaxPos);
     memcpy(T.acl_slot4, H.acl_slot4, kAclMaxPos);
     memcpy(T.acl_slot6, H.acl_slot6, kAclMaxPos);
-    T.counters = h->d_counters;
+    T.counters = counters;
+}
+
+void bind_tables(sfc_handle* h) {
+    ImageHeader H;
+    cudaMemcpy(&H, h->d_image, sizeof(H), cudaMemcpyDeviceToHost);
+    fill_tables(h->T, H, h->d_image, h->d_counters, h->probe_mode);
     h->epoch = H.epoch;
     h->flow_first[0] = H.flow4_first;
     h->flow_first[1] = H.flow6_first;
@@ -616,8 +619,7 @@ int sfc_table_export(const sfc_handle* hc, void* buf, size_t len) {
 
 int sfc_table_import(sfc_handle* h, const void* buf, size_t len) {
     if (!h || !buf) return -EINVAL;
-    std::string err;
-    if (!validate_image((const uint8_t*)buf, len, err)) return fail(h, -EINVAL, "sfc_table_import: %s", err.c_str());
+    if (const char* why = validate_image((const uint8_t*)buf, len)) return fail(h, -EINVAL, "sfc_table_import: %s", why);
     if (h->offline()) {
         h->host_image.assign((const uint8_t*)buf, (const uint8_t*)buf + len);
         h->image_bytes = len;

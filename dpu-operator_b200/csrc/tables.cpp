@@ -535,38 +535,29 @@ bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& imag
     return true;
 }
 
-bool validate_image(const uint8_t* img, size_t len, std::string& err) {
-    if (len < kImageHeaderBytes) {
-        err = "image: shorter than its header";
-        return false;
-    }
+const char* validate_image(const uint8_t* img, size_t len) {
+    if (len < kImageHeaderBytes) return "image: shorter than its header";
     ImageHeader H;
     memcpy(&H, img, sizeof(H));
-    if (H.magic != kImageMagic || H.version != kImageVersion) {
-        err = "image: bad magic or version";
-        return false;
-    }
-    if (H.total_bytes != len || H.header_bytes != kImageHeaderBytes) {
-        err = "image: size field does not match the buffer length";
-        return false;
-    }
+    if (H.magic != kImageMagic || H.version != kImageVersion) return "image: bad magic or version";
+    if (H.total_bytes != len || H.header_bytes != kImageHeaderBytes)
+        return "image: size field does not match the buffer length";
     auto inside = [&](uint64_t off, uint64_t bytes) { return off >= kImageHeaderBytes && off + bytes <= len; };
     bool ok = inside(H.flow4_off, (uint64_t)H.flow4_nbuckets * kFlow4BucketBytes) &&
               inside(H.flow6_off, (uint64_t)H.flow6_nbuckets * kFlow6BucketBytes) &&
               inside(H.l2x_off, ((uint64_t)H.l2x_mask + 1) * sizeof(L2Entry)) &&
               ((H.l2x_mask & (H.l2x_mask + 1)) == 0) && inside(H.l2w_off, (uint64_t)H.l2w_n * sizeof(L2Wild)) &&
-              inside(H.lpm4_root_off, 65536 * 4) &&
-              inside(H.lpm4_nodes_off, (uint64_t)H.lpm4_nnodes * 1024) && inside(H.lpm6_root_off, 65536 * 4) &&
-              inside(H.lpm6_nodes_off, (uint64_t)H.lpm6_nnodes * 1024) && inside(H.lpm4_nh_off, 8) &&
-              inside(H.lpm6_nh_off, 8) && H.flow4_nhash >= 1 && H.flow4_nhash <= kMaxHashes &&
-              H.flow6_nhash >= 1 && H.flow6_nhash <= kMaxHashes && H.flow4_nbuckets && H.flow6_nbuckets &&
-              H.acl_npos4 <= kAclMaxPos && H.acl_npos6 <= kAclMaxPos && H.acl_nrules <= SFC_MAX_ACL_RULES;
+              inside(H.lpm4_root_off, 65536 * 4) && inside(H.lpm4_nodes_off, (uint64_t)H.lpm4_nnodes * 1024) &&
+              inside(H.lpm6_root_off, 65536 * 4) && inside(H.lpm6_nodes_off, (uint64_t)H.lpm6_nnodes * 1024) &&
+              inside(H.lpm4_nh_off, 8) && inside(H.lpm6_nh_off, 8) && H.flow4_nhash >= 1 &&
+              H.flow4_nhash <= kMaxHashes && H.flow6_nhash >= 1 && H.flow6_nhash <= kMaxHashes && H.flow4_nbuckets &&
+              H.flow6_nbuckets && H.acl_npos4 <= kAclMaxPos && H.acl_npos6 <= kAclMaxPos &&
+              H.acl_nrules <= SFC_MAX_ACL_RULES;
     if (ok && H.acl_nrules)
         ok = inside(H.acl_bv_off, (uint64_t)H.acl_nstored * 256 * H.acl_nwords * 4) &&
              inside(H.acl_base_off, (uint64_t)2 * H.acl_nwords * 4) &&
              inside(H.acl_rule_off, (uint64_t)H.acl_nrules * 4);
-    if (!ok) err = "image: a section lies outside the buffer or a field is out of range";
-    return ok;
+    return ok ? nullptr : "image: a section lies outside the buffer or a field is out of range";
 }
 
 }  // namespace sfc

@@ -95,6 +95,7 @@ bool flow_from_key(const sfc_flow_key& k, const sfc_flow_action& a, FlowRec& out
 bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& image, std::string& err);
 
 // Structural validation of an image received from elsewhere (import / broadcast).
-bool validate_image(const uint8_t* img, size_t len, std::string& err);
+// Returns nullptr if the image is sound, else a static message.  Touches no heap.
+const char* validate_image(const uint8_t* img, size_t len);
 
 }  // namespace sfc
