@@ -18,6 +18,8 @@ from .capi import (  # noqa: F401
     LIB_PATH,
     Dataplane,
     SfcError,
+    STATIC_AREA_BYTES,
+    classify_static,
     gen_acl_rules,
     gen_flows,
     gen_mac,
@@ -46,4 +48,6 @@ __all__ = [
     "gen_acl_rules",
     "gen_mac",
     "result_fields",
+    "classify_static",
+    "STATIC_AREA_BYTES",
 ]

@@ -90,6 +90,7 @@ def _load():
         "sfc_counters_device_ptr": (vp, [vp]),
         "sfc_launch_count": (C.c_uint64, [vp]),
         "sfc_last_kernel_ms": (C.c_float, [vp]),
+        "sfc_classify_static": (C.c_int, [C.c_int, vp, C.c_size_t, vp, vp, vp, C.c_size_t, vp, C.c_char_p, C.c_size_t]),
         "sfc_gen_packets": (C.c_int, [vp, vp, C.c_uint64, C.c_size_t, vp, vp, vp]),
         "sfc_gen_packets_host": (None, [vp, C.c_uint64, C.c_size_t, vp, vp]),
         "sfc_gen_flows": (None, [vp, C.c_uint32, C.c_size_t, vp, vp]),
@@ -303,6 +304,24 @@ class Dataplane:
 
     def gen_packets(self, spec: np.ndarray, first: int, n: int, hdr_ptr: int, in_port_ptr: int, stream: int = 0):
         self._chk(lib.sfc_gen_packets(self._h, _ptr(spec), first, n, hdr_ptr, in_port_ptr, stream))
+
+
+STATIC_AREA_BYTES = 4 << 20
+
+
+def classify_static(device: int, image, hdr_ptr: int, in_port_ptr: int, result_ptr: int, n: int, stream: int = 0):
+    """``sfc_classify_static``: classify with no handle and no allocation.  ``image`` is a host
+    uint8 array holding a table image, or None to reuse the one the previous call left on the
+    device.  Raises SfcError with the library's message on failure."""
+    err = C.create_string_buffer(512)
+    if image is None:
+        ptr, nbytes = None, 0
+    else:
+        image = np.ascontiguousarray(image, dtype=np.uint8)
+        ptr, nbytes = image.ctypes.data, image.size
+    rc = lib.sfc_classify_static(device, ptr, nbytes, hdr_ptr, in_port_ptr, result_ptr, n, stream, err, len(err))
+    if rc:
+        raise SfcError(rc, err.value.decode())
 
 
 # ---------------------------------------------------------------- synthetic workload (host) ----

@@ -761,6 +761,139 @@ void* sfc_counters_device_ptr(sfc_handle* h) { return h ? (void*)h->d_counters :
 uint64_t sfc_launch_count(const sfc_handle* h) { return h ? h->launches : 0; }
 float sfc_last_kernel_ms(const sfc_handle* h) { return h ? h->last_kernel_ms : -1.f; }
 
+// =================================================================== no-allocation call ==
+// Scratch of sfc_classify_static: [0, 256) tile-ticket words of the classify kernel, then the table
+// image.  One copy per GPU that loads this library, resident until the process exits.
+static __device__ __align__(256) unsigned char g_static_area[SFC_STATIC_AREA_BYTES];
+
+namespace {
+constexpr size_t kStaticTicketBytes = 256;
+constexpr int kStaticMaxDevices = 64;
+struct StaticDev {
+    bool ready = false;
+    unsigned char* area = nullptr;  // device address of g_static_area ON THIS DEVICE
+    int sm_count = 0;
+    int ctas_per_sm[2] = {0, 0};    // [no ACL, ACL]
+    EncodeTiledFn encode = nullptr;
+    bool resident = false;          // an image was copied in by an earlier call
+    ImageHeader header;
+};
+StaticDev g_static_dev[kStaticMaxDevices];
+
+int static_fail(char* errbuf, size_t errlen, int code, const char* fmt, ...) {
+    if (errbuf && errlen) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(errbuf, errlen, fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+// Once per device, with that device current.  In host code `g_static_area` is only a stand-in for
+// the symbol, not a device address: the address a kernel may use comes from cudaGetSymbolAddress.
+int static_setup(int device, StaticDev& d, char* errbuf, size_t errlen) {
+    int major = 0;
+    cudaError_t e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+    if (e != cudaSuccess || major < 10)
+        return static_fail(errbuf, errlen, -ENODEV, "device %d is not a compute-capability 10.x GPU", device);
+    cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, device);
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_area);
+    if (e != cudaSuccess || !p)
+        return static_fail(errbuf, errlen, -EIO, "cudaGetSymbolAddress(static area): %s", cudaGetErrorString(e));
+    d.area = (unsigned char*)p;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn)
+        return static_fail(errbuf, errlen, -ENOSYS, "driver lacks cuTensorMapEncodeTiled");
+    d.encode = (EncodeTiledFn)fn;
+    const void* kerns[2] = {(const void*)classify_kernel<kTile, kStages, false, false>,
+                            (const void*)classify_kernel<kTile, kStages, false, true>};
+    const int smem[2] = {SmemLayout<kTile, kStages, false>::kBytes, SmemLayout<kTile, kStages, true>::kBytes};
+    for (int v = 0; v < 2; ++v) {
+        e = cudaFuncSetAttribute(kerns[v], cudaFuncAttributeMaxDynamicSharedMemorySize, smem[v]);
+        if (e == cudaSuccess)
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.ctas_per_sm[v], kerns[v], kTile + 32, smem[v]);
+        if (e != cudaSuccess || d.ctas_per_sm[v] < 1)
+            return static_fail(errbuf, errlen, -EIO, "classify kernel set-up: %s", cudaGetErrorString(e));
+    }
+    d.ready = true;
+    return 0;
+}
+}  // namespace
+
+extern "C" int sfc_classify_static(int device, const void* image_host, size_t image_bytes, const void* hdr,
+                                   const uint16_t* in_port, uint64_t* result, size_t n, void* cuda_stream,
+                                   char* errbuf, size_t errlen) {
+    if (errbuf && errlen) errbuf[0] = 0;
+    if (device < 0 || device >= kStaticMaxDevices)
+        return static_fail(errbuf, errlen, -EINVAL, "device ordinal %d out of range", device);
+    if (n > (1ull << 31)) return static_fail(errbuf, errlen, -EINVAL, "at most 2^31 packets per call");
+    if (n && (!hdr || !in_port || !result)) return static_fail(errbuf, errlen, -EINVAL, "null packet buffer");
+    if (((uintptr_t)hdr & 15) != 0) return static_fail(errbuf, errlen, -EINVAL, "hdr must be 16-byte aligned");
+    // the size limit is checked before any CUDA call
+    const size_t max_image = SFC_STATIC_AREA_BYTES - kStaticTicketBytes;
+    if (image_host) {
+        if (image_bytes > max_image)
+            return static_fail(errbuf, errlen, -E2BIG,
+                               "table image of %zu bytes does not fit the static device area: at most %zu bytes "
+                               "(SFC_STATIC_AREA_BYTES %u minus %zu for kernel scratch); use sfc_classify with a handle",
+                               image_bytes, max_image, (unsigned)SFC_STATIC_AREA_BYTES, kStaticTicketBytes);
+        if (const char* why = validate_image((const uint8_t*)image_host, image_bytes))
+            return static_fail(errbuf, errlen, -EINVAL, "%s", why);
+    }
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device >= count)
+        return static_fail(errbuf, errlen, -ENODEV, "no CUDA device %d (there is no CPU fallback)", device);
+    DeviceGuard g(device);
+    StaticDev& d = g_static_dev[device];
+    if (!d.ready) {
+        int rc = static_setup(device, d, errbuf, errlen);
+        if (rc) return rc;
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    unsigned char* image_dev = d.area + kStaticTicketBytes;
+    cudaError_t e;
+    if (image_host) {
+        e = cudaMemcpyAsync(image_dev, image_host, image_bytes, cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) return static_fail(errbuf, errlen, -EIO, "image copy: %s", cudaGetErrorString(e));
+        memcpy(&d.header, image_host, sizeof(ImageHeader));
+        d.resident = true;
+    } else if (!d.resident) {
+        return static_fail(errbuf, errlen, -ENOENT, "image_host is NULL but no earlier call left an image on device %d", device);
+    }
+    if (n == 0) return 0;
+    // the array keeps the previous call's contents: the ticket words must start at zero
+    e = cudaMemsetAsync(d.area, 0, kStaticTicketBytes, st);
+    if (e != cudaSuccess) return static_fail(errbuf, errlen, -EIO, "scratch clear: %s", cudaGetErrorString(e));
+    DevTables T{};
+    fill_tables(T, d.header, image_dev, nullptr, -1);
+    CUtensorMap map;
+    cuuint64_t dims[2] = {16, (cuuint64_t)n};
+    cuuint64_t strides[1] = {64};
+    cuuint32_t box[2] = {16, (cuuint32_t)(kTile < 256 ? kTile : 256)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = d.encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(hdr), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return static_fail(errbuf, errlen, -EIO, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    const bool acl = T.acl_nrules > 0;
+    const uint64_t n_tiles = (n + kTile - 1) / kTile;
+    const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)d.sm_count * d.ctas_per_sm[acl ? 1 : 0]);
+    uint32_t* ticket = (uint32_t*)d.area;
+    uint32_t* stale = ticket + 1;  // the kernel clears this word for a later launch; unused here
+    if (acl)
+        classify_kernel<kTile, kStages, false, true><<<grid, kTile + 32, SmemLayout<kTile, kStages, true>::kBytes, st>>>(
+            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, stale, 0u, T);
+    else
+        classify_kernel<kTile, kStages, false, false><<<grid, kTile + 32, SmemLayout<kTile, kStages, false>::kBytes, st>>>(
+            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, stale, 0u, T);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return static_fail(errbuf, errlen, -EIO, "kernel launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
 // =================================================================== generator ===========
 int sfc_gen_packets(sfc_handle* h, const sfc_gen_spec* spec, uint64_t first, size_t n, void* hdr_dev,
                     uint16_t* in_port_dev, void* cuda_stream) {

@@ -286,6 +286,47 @@ uint64_t sfc_launch_count(const sfc_handle* h);
  * (CUDA events on the library's stream); < 0 if none. */
 float sfc_last_kernel_ms(const sfc_handle* h);
 
+/* ---------------------------------------------------------------- no-allocation call ---- */
+
+/* Classify without ever allocating.  This entry point has no counterpart in the reference.
+ *
+ * Who needs it: callers that are not allowed to obtain device memory at the moment they have
+ * packets to classify — a dataplane thread that runs under a fixed memory budget handed out at
+ * start-up, a shim loaded into a process whose allocator is owned by another runtime, a polling
+ * loop that must not take the driver's allocation locks (cudaMalloc/cudaFree serialise the whole
+ * device).  sfc_create/sfc_commit call cudaMalloc for the table image and the kernel's scratch;
+ * this call does neither.  It takes no handle: the caller passes the table image (as built by an
+ * OFFLINE handle's sfc_commit + sfc_table_export, or exported from any handle) in HOST memory
+ * together with the packet buffers, and the library keeps what it needs on the GPU in a fixed
+ * array that is part of the library image itself:
+ *
+ *   SFC_STATIC_AREA_BYTES of device memory per GPU, present on every GPU that loads the library
+ *   from load until the process exits.  The first 256 bytes are the classify kernel's tile-ticket
+ *   scratch; the rest holds the table image, so an image may be at most
+ *   SFC_STATIC_AREA_BYTES - 256 bytes (a steering set plus tens of thousands of flows).  A larger
+ *   image is refused with -E2BIG and a message naming both sizes; nothing is truncated.
+ *
+ * Behaviour
+ *   - hdr / in_port / result are DEVICE pointers as for sfc_classify; image_host is a HOST pointer.
+ *     Pass image_host == NULL to classify against the image the previous call left on that device.
+ *   - asynchronous on cuda_stream; results are bit-identical to sfc_classify with the same image.
+ *   - the FIRST call on each device also does one-time set-up (looks up the array's device
+ *     address, raises the kernel's shared-memory limit).  Make that first call before starting any
+ *     stream capture on the device; later calls only copy, clear and launch.
+ *   - every call on a device shares the one array and it keeps what the last call left there.  The
+ *     call clears the ticket words itself (they must start at zero) and overwrites the image when
+ *     one is passed; it does not and cannot protect the array from a second call running at the
+ *     same time.  Two calls whose GPU work overlaps — different streams, or threads — race on the
+ *     tickets and on the image: run them on one stream, or order them with events.
+ *   - counters (SFC_F_COUNTERS) are not available here: they live in handle-owned memory.
+ *   - on failure a negative errno is returned and, if errbuf != NULL, a NUL-terminated message of
+ *     at most errlen bytes is written to it.  Never calls cudaMalloc, cudaFree, or anything that
+ *     allocates on its behalf. */
+#define SFC_STATIC_AREA_BYTES (4u << 20)
+int sfc_classify_static(int device, const void* image_host, size_t image_bytes, const void* hdr,
+                        const uint16_t* in_port, uint64_t* result, size_t n, void* cuda_stream,
+                        char* errbuf, size_t errlen);
+
 /* ---------------------------------------------------------------- synthetic traffic ----- */
 
 /* Fill device buffers with the deterministic synthetic workload of SURVEY.md §8(d) (counter-based
