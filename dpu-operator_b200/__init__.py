@@ -19,6 +19,7 @@ from .capi import (  # noqa: F401
     Dataplane,
     SfcError,
     STATIC_AREA_BYTES,
+    VspServer,
     classify_static,
     gen_acl_rules,
     gen_flows,
@@ -49,5 +50,6 @@ __all__ = [
     "gen_mac",
     "result_fields",
     "classify_static",
+    "VspServer",
     "STATIC_AREA_BYTES",
 ]

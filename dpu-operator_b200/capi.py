@@ -97,6 +97,18 @@ def _load():
         "sfc_gen_mac": (None, [C.c_uint32, vp]),
         "sfc_gen_prefix": (None, [vp, C.c_int, C.c_uint32, vp, C.POINTER(C.c_int), u16p]),
         "sfc_gen_acl_rule": (None, [vp, C.c_uint32, vp]),
+        # include/b200vsp.h
+        "vsp_create": (C.c_int, [C.c_int, C.c_char_p, C.POINTER(vp)]),
+        "vsp_destroy": (C.c_int, [vp]),
+        "vsp_last_error": (C.c_char_p, [vp]),
+        "vsp_add_nf_device": (C.c_int, [vp, C.c_char_p, C.c_char_p]),
+        "vsp_init": (C.c_int, [vp, C.c_int]),
+        "vsp_create_bridge_port": (C.c_int, [vp, C.c_char_p, vp, C.c_char_p, C.c_size_t]),
+        "vsp_delete_bridge_port": (C.c_int, [vp, C.c_char_p]),
+        "vsp_create_network_function": (C.c_int, [vp, C.c_char_p, C.c_char_p]),
+        "vsp_delete_network_function": (C.c_int, [vp, C.c_char_p, C.c_char_p]),
+        "vsp_flow_dump": (C.c_long, [vp, C.c_char_p, C.c_size_t]),
+        "vsp_dataplane": (vp, [vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)  # AttributeError here = the header and the library disagree
@@ -127,17 +139,22 @@ def _mac_buf(mac):
 class Dataplane:
     """One ``sfc_handle``.  Method names are the C entry points without the ``sfc_`` prefix."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device: int = 0, _borrowed=None):
+        self._owned = _borrowed is None
+        self.device = device
+        if _borrowed is not None:
+            self._h = C.c_void_p(_borrowed)
+            return
         h = C.c_void_p()
         rc = lib.sfc_create(device, C.byref(h))
         if rc:
             raise SfcError(rc, "sfc_create failed (no CUDA device of compute capability 10.x? there is no CPU fallback)")
         self._h = h
-        self.device = device
 
     def close(self):
         if getattr(self, "_h", None):
-            lib.sfc_destroy(self._h)
+            if self._owned:
+                lib.sfc_destroy(self._h)
             self._h = None
 
     def __del__(self):
@@ -304,6 +321,60 @@ class Dataplane:
 
     def gen_packets(self, spec: np.ndarray, first: int, n: int, hdr_ptr: int, in_port_ptr: int, stream: int = 0):
         self._chk(lib.sfc_gen_packets(self._h, _ptr(spec), first, n, hdr_ptr, in_port_ptr, stream))
+
+
+class VspServer:
+    """The host-side mirror of the reference's Marvell vendor plugin (include/b200vsp.h).  Method
+    names are the RPCs of dpu-api/api.proto and OPI BridgePortService."""
+
+    def __init__(self, device: int = 0, rpm_port: str = "rpm0"):
+        v = C.c_void_p()
+        rc = lib.vsp_create(device, rpm_port.encode(), C.byref(v))
+        if rc:
+            raise SfcError(rc, "vsp_create failed")
+        self._v, self.device = v, device
+
+    def __del__(self):
+        if getattr(self, "_v", None):
+            lib.vsp_destroy(self._v)
+            self._v = None
+
+    def _chk(self, rc):
+        if rc < 0:
+            raise SfcError(rc, lib.vsp_last_error(self._v).decode())
+
+    def add_nf_device(self, nf_mac: str, dp_interface: str):
+        self._chk(lib.vsp_add_nf_device(self._v, nf_mac.encode(), dp_interface.encode()))
+
+    def Init(self, dpu_mode: bool = True):
+        self._chk(lib.vsp_init(self._v, int(dpu_mode)))
+
+    def CreateBridgePort(self, name: str, mac: bytes) -> str:
+        out = C.create_string_buffer(128)
+        self._chk(lib.vsp_create_bridge_port(self._v, name.encode(), _mac_buf(mac), out, len(out)))
+        return out.value.decode()
+
+    def DeleteBridgePort(self, name: str):
+        self._chk(lib.vsp_delete_bridge_port(self._v, name.encode()))
+
+    def CreateNetworkFunction(self, input_mac: str, output_mac: str):
+        self._chk(lib.vsp_create_network_function(self._v, input_mac.encode(), output_mac.encode()))
+
+    def DeleteNetworkFunction(self, input_mac: str, output_mac: str):
+        self._chk(lib.vsp_delete_network_function(self._v, input_mac.encode(), output_mac.encode()))
+
+    def flow_dump(self) -> list[str]:
+        need = lib.vsp_flow_dump(self._v, None, 0)
+        buf = C.create_string_buffer(need)
+        lib.vsp_flow_dump(self._v, buf, need)
+        return [x for x in buf.value.decode().split("\n") if x]
+
+    @property
+    def dataplane(self) -> "Dataplane":
+        h = lib.vsp_dataplane(self._v)
+        if not h:
+            raise SfcError(-19, "VSP has no dataplane yet (call Init(dpu_mode=True))")
+        return Dataplane(self.device, _borrowed=h)
 
 
 STATIC_AREA_BYTES = 4 << 20

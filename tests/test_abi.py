@@ -9,9 +9,12 @@ from common import ROOT, sfc
 
 
 def declared_symbols():
-    text = open(os.path.join(ROOT, "include", "b200sfc.h")).read()
-    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(sfc_[a-z0-9_]+)\s*\(", text)))
+    syms = set()
+    for name in sorted(os.listdir(os.path.join(ROOT, "include"))):
+        text = open(os.path.join(ROOT, "include", name)).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        syms |= set(re.findall(r"\b((?:sfc|vsp)_[a-z0-9_]+)\s*\(", text))
+    return sorted(syms)
 
 
 def test_header_declares_something():

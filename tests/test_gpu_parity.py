@@ -287,3 +287,42 @@ def test_repeated_launches_are_stable(torch_cuda):
         torch.cuda.synchronize()
         bad = int((res != want).sum().item())
         assert bad == 0, f"iteration {it}: {bad} results differ from the oracle"
+
+
+def test_vsp_replay_on_the_gpu(torch_cuda):
+    """configs[0] end to end: the rules programmed through the VSP mirror (CreateBridgePort /
+    CreateNetworkFunction, the reference's own RPCs) steer synthetic traffic on the GPU exactly as
+    the oracle says when fed the dumped rule strings."""
+    import json
+    import os
+
+    from common import ROOT
+
+    G = json.load(open(os.path.join(ROOT, "tests", "golden", "replay_rules.json")))
+    mac = lambda s: bytes(int(x, 16) for x in s.split(":"))  # noqa: E731
+    v = sfc.VspServer(0, G["rpm_port"])
+    for m, ifc in zip(G["nf_macs"], G["dp_interfaces"]):
+        v.add_nf_device(m, ifc)
+    v.Init(True)
+    for i, m in enumerate(G["vf_macs"][:-1]):
+        v.CreateBridgePort(f"host0-{i}", mac(m))
+    v.CreateNetworkFunction(*G["nf_macs"])
+    v.CreateBridgePort(f"host0-{len(G['vf_macs']) - 1}", mac(G["vf_macs"][-1]))  # one pod arrives after the chain
+    assert sorted(v.flow_dump()) == sorted(G["rules_ports_then_nf"])
+    dp = v.dataplane
+    orc = Oracle()
+    for rid, line in enumerate(v.flow_dump()):
+        f = dict(kv.split("=", 1) for kv in line.split(",") if "=" in kv)
+        inp = dp.port_lookup(f["in_port"])
+        out = inp if line.endswith("actions=in_port") else dp.port_lookup(line.rsplit("output:", 1)[1])
+        orc.l2_add(inp, out, mac(f["dl_dst"]) if "dl_dst" in f else None, int(f.get("priority", consts.PRIO_MAC)), rid)
+    spec = sfc.make_gen_spec(n_flows=0, n_ports=len(G["ports"]) + 2, n_macs=10, nonip_permille=300, v6_permille=200,
+                             vlan_permille=200)
+    hdr, ports = sfc.gen_packets_host(spec, 0, 100000)
+    got = classify_dev(torch_cuda, dp, hdr, ports)
+    want = orc.classify(hdr, ports)
+    # rule ids differ (the library numbers rules in add order, the dump is in list order): compare decisions
+    ga, gn, gp, gs, _ = sfc.result_fields(got)
+    wa, wn, wp, ws, _ = sfc.result_fields(want)
+    assert np.array_equal(ga, wa) and np.array_equal(gp, wp) and np.array_equal(gs, ws)
+    assert (gs == consts.STAGE_L2_EXACT).sum() > 0 and (gs == consts.STAGE_L2_WILD).sum() > 0 and (gs == consts.STAGE_MISS).sum() > 0
