@@ -23,7 +23,8 @@ using namespace sfc;
 namespace {
 constexpr int kTile = 128;
 constexpr int kStages = 2;
-constexpr int kTicketRing = 32;      // a launch uses slot seq % 32 and clears slot (seq + 16) % 32
+constexpr int kTicketRing = 32;      // a launch uses slot seq % 32; slots are 32 bytes apart and self-resetting
+constexpr int kTicketStride = 8;     // u32 words per slot: {draw counter, finished producers, pad}
 constexpr size_t kHostChunk = 1u << 18;  // packets per pipelined chunk in sfc_classify_host
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -128,6 +129,9 @@ void fill_tables(DevTables& T, const ImageHeader& H, const uint8_t* b, unsigned 
     T.acl_bv = (const uint32_t*)(b + H.acl_bv_off);
     T.acl_base = (const uint32_t*)(b + H.acl_base_off);
     T.acl_rule = (const uint32_t*)(b + H.acl_rule_off);
+    T.acl_sum = (const uint32_t*)(b + H.acl_sum_off);
+    T.acl_basesum = (const uint32_t*)(b + H.acl_basesum_off);
+    T.acl_nsw = H.acl_nsw;
     T.acl_nrules = H.acl_nrules;
     T.acl_nwords = H.acl_nwords;
     T.acl_npos4 = H.acl_npos4;
@@ -187,8 +191,7 @@ int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_
     if (r != CUDA_SUCCESS) return fail(h, -EIO, "cuTensorMapEncodeTiled failed (%d)", (int)r);
     uint64_t n_tiles = (n + TILE - 1) / TILE;
     uint64_t grid = std::min<uint64_t>(n_tiles, (uint64_t)h->sm_count * h->ctas_per_sm[slot]);
-    uint32_t* ticket = h->d_tickets + (h->launches % kTicketRing);
-    uint32_t* stale = h->d_tickets + ((h->launches + kTicketRing / 2) % kTicketRing);
+    uint32_t* ticket = h->d_tickets + (h->launches % kTicketRing) * kTicketStride;
     uint32_t overlap = (flags & SFC_F_OVERLAP) ? 1u : 0u;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
@@ -200,8 +203,8 @@ int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = overlap ? 1 : 0;
-    CUDA_TRY(h, cudaLaunchKernelEx(&cfg, kern, map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, stale,
-                                   overlap, h->T));
+    CUDA_TRY(h, cudaLaunchKernelEx(&cfg, kern, map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, overlap,
+                                   h->T));
     ++h->launches;
     return 0;
 }
@@ -250,7 +253,7 @@ __global__ void gen_kernel(sfc_gen_spec spec, uint64_t first, uint64_t n, uint8_
 // =================================================================== life cycle ==========
 extern "C" {
 
-const char* sfc_version(void) { return "b200sfc 0.1 (image v3)"; }
+const char* sfc_version(void) { return "b200sfc 0.2 (image v5)"; }
 
 int sfc_create(int device_ordinal, sfc_handle** out) {
     if (!out) return -EINVAL;
@@ -283,8 +286,8 @@ int sfc_create(int device_ordinal, sfc_handle** out) {
     if (const char* tune = getenv("SFC_TUNE")) sscanf(tune, "%d,%d", &h->tune_tile, &h->tune_stages);
     if (cudaMalloc(&h->d_counters, SFC_CNT_TOTAL * sizeof(uint64_t)) != cudaSuccess ||
         cudaMemset(h->d_counters, 0, SFC_CNT_TOTAL * sizeof(uint64_t)) != cudaSuccess ||
-        cudaMalloc(&h->d_tickets, kTicketRing * sizeof(uint32_t)) != cudaSuccess ||
-        cudaMemset(h->d_tickets, 0, kTicketRing * sizeof(uint32_t)) != cudaSuccess) {
+        cudaMalloc(&h->d_tickets, kTicketRing * kTicketStride * sizeof(uint32_t)) != cudaSuccess ||
+        cudaMemset(h->d_tickets, 0, kTicketRing * kTicketStride * sizeof(uint32_t)) != cudaSuccess) {
         delete h;
         return -ENOMEM;
     }
@@ -881,14 +884,13 @@ extern "C" int sfc_classify_static(int device, const void* image_host, size_t im
     const bool acl = T.acl_nrules > 0;
     const uint64_t n_tiles = (n + kTile - 1) / kTile;
     const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)d.sm_count * d.ctas_per_sm[acl ? 1 : 0]);
-    uint32_t* ticket = (uint32_t*)d.area;
-    uint32_t* stale = ticket + 1;  // the kernel clears this word for a later launch; unused here
+    uint32_t* ticket = (uint32_t*)d.area;  // {draw counter, finished producers}: cleared above, reset by the kernel too
     if (acl)
         classify_kernel<kTile, kStages, false, true><<<grid, kTile + 32, SmemLayout<kTile, kStages, true>::kBytes, st>>>(
-            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, stale, 0u, T);
+            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, 0u, T);
     else
         classify_kernel<kTile, kStages, false, false><<<grid, kTile + 32, SmemLayout<kTile, kStages, false>::kBytes, st>>>(
-            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, stale, 0u, T);
+            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, 0u, T);
     e = cudaGetLastError();
     if (e != cudaSuccess) return static_fail(errbuf, errlen, -EIO, "kernel launch: %s", cudaGetErrorString(e));
     return 0;

@@ -41,7 +41,9 @@ struct DevTables {
     const uint32_t* acl_bv;
     const uint32_t* acl_base;  // [2][nwords]
     const uint32_t* acl_rule;
-    uint32_t acl_nrules, acl_nwords, acl_npos4, acl_npos6;
+    const uint32_t* acl_sum;      // [stored position][byte value][nsw]
+    const uint32_t* acl_basesum;  // [2][nsw]
+    uint32_t acl_nrules, acl_nwords, acl_npos4, acl_npos6, acl_nsw;
     uint8_t acl_pos4[kAclMaxPos], acl_pos6[kAclMaxPos], acl_slot4[kAclMaxPos], acl_slot6[kAclMaxPos];
     unsigned long long* counters;
 };
@@ -265,8 +267,8 @@ template <int TILE, int STAGES, bool COUNTERS, bool ACL>
 __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
                                                               const uint16_t* __restrict__ in_port,
                                                               uint64_t* __restrict__ result, uint32_t n,
-                                                              uint32_t n_tiles, uint32_t* tile_counter,
-                                                              uint32_t* stale_counter, uint32_t overlap,
+                                                              uint32_t n_tiles, uint32_t* ticket,
+                                                              uint32_t overlap,
                                                               const __grid_constant__ DevTables T) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -297,16 +299,17 @@ __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_consta
         // Tiles are handed out dynamically: the first one is the CTA's own index, the rest come from
         // a global ticket counter, so SMs that run slow (far L2 die, unlucky probes) simply take
         // fewer tiles.  The draw for the next tile is issued before waiting on the current slot.
+        // ticket[0] is the draw counter, ticket[1] counts producers that have finished; the last one
+        // to finish puts both back to zero, so the slot is ready for its next launch (or graph replay).
         if (tid == TILE) {
             if (overlap) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-            if (blockIdx.x == 0) *stale_counter = 0;  // the ticket counter of a launch 16 calls from now
             uint64_t pol = policy_evict_first();
             uint32_t tile = blockIdx.x;
             for (uint32_t it = 0;; ++it) {
                 const uint32_t s = it % STAGES, use = it / STAGES;
                 const bool have = tile < n_tiles;
                 uint32_t next = 0;
-                if (have) next = gridDim.x + atomicAdd(tile_counter, 1u);
+                if (have) next = gridDim.x + atomicAdd(ticket, 1u);
                 if (use > 0) mbar_wait(empty + s, (use - 1) & 1);
                 tile_of[s] = have ? tile : 0xFFFFFFFFu;
                 if (!have) {
@@ -318,6 +321,11 @@ __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_consta
                 for (int r = 0; r < TILE; r += kBoxRows)  // a TMA box is at most 256 rows
                     tma_load_tile(tiles + s * TILE * 64 + r * 64, &hdr_map, 0, (int)(tile * TILE) + r, full + s, pol);
                 tile = next;
+            }
+            __threadfence();
+            if (atomicAdd(ticket + 1, 1u) == gridDim.x - 1) {  // every producer has made its last draw
+                ticket[0] = 0;
+                ticket[1] = 0;
             }
             // keep stream order intact when launches overlap: do not retire before the previous grid has
             if (overlap) asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -366,55 +374,59 @@ __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_consta
         uint32_t rhi = kResMissHi, rlo = kResMissLo;
         bool done = !live;  // lanes past the end of the batch hold zero-filled records
 
-        // ---- stage 1: ACL (warp-cooperative byte-sliced bit vectors) ----
+        // ---- stage 1: ACL — byte-sliced bit vectors with an aggregate level, one packet per thread ----
+        // Rules are sorted by (priority desc, id asc), so the first set bit of the AND over the packet's
+        // key bytes is the winner.  The 32-bit summaries (one bit per 32-rule word, L1-resident) are
+        // ANDed first; only words whose summary survives are ANDed in full, in order, until one is
+        // non-zero.  Exact for arbitrary ternary masks; the key words sit in shared memory because the
+        // active byte positions are table data (dynamic indexing).
         if (ACL) {
-            uint32_t* q = aclq + (tid >> 5) * (kAclKeyWords * 32);
-            q[0 * 32 + lane] = (port << 16) | (k.meta >> 8);
-            q[1 * 32 + lane] = (k.ip_ver << 24) | ((k.meta & 0xFFu) << 16) | (k.ports >> 16);
-            q[2 * 32 + lane] = k.ports << 16;
+            uint32_t* q = aclq + (tid >> 5) * (kAclKeyWords * 32) + lane;
+            q[0 * 32] = (port << 16) | (k.meta >> 8);
+            q[1 * 32] = (k.ip_ver << 24) | ((k.meta & 0xFFu) << 16) | (k.ports >> 16);
+            q[2 * 32] = k.ports << 16;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                q[(3 + i) * 32 + lane] = k.sip[i];
-                q[(7 + i) * 32 + lane] = k.dip[i];
+                q[(3 + i) * 32] = k.sip[i];
+                q[(7 + i) * 32] = k.dip[i];
             }
-            __syncwarp();
-            uint32_t todo = __ballot_sync(0xFFFFFFFFu, live && is_ip);
-            uint32_t my_hit = 0xFFFFFFFFu;
-            while (todo) {
-                int j = __ffs(todo) - 1;
-                todo &= todo - 1;
-                bool v6 = (q[1 * 32 + j] >> 24) == 6u;
+            if (live && is_ip) {
+                const bool v6 = k.ip_ver == 6u;
                 const uint8_t* pos = v6 ? T.acl_pos6 : T.acl_pos4;
                 const uint8_t* slot = v6 ? T.acl_slot6 : T.acl_slot4;
-                uint32_t npos = v6 ? T.acl_npos6 : T.acl_npos4;
-                uint32_t best = 0xFFFFFFFFu;
-                for (uint32_t wbase = 0; wbase < T.acl_nwords && best == 0xFFFFFFFFu; wbase += 32) {
-                    uint32_t wi = wbase + lane;
-                    bool in = wi < T.acl_nwords;
-                    uint32_t acc = in ? __ldg(T.acl_base + (v6 ? T.acl_nwords : 0) + wi) : 0u;
-                    for (uint32_t p = 0; p < npos; ++p) {
-                        uint32_t kb = pos[p];
-                        uint32_t val = (q[(kb >> 2) * 32 + j] >> (24 - 8 * (kb & 3))) & 0xFFu;
-                        if (in) acc &= __ldg(T.acl_bv + ((size_t)slot[p] * 256 + val) * T.acl_nwords + wi);
-                        if ((p & 3) == 3 && __ballot_sync(0xFFFFFFFFu, acc != 0) == 0) break;
+                const uint32_t npos = v6 ? T.acl_npos6 : T.acl_npos4;
+                const uint32_t nw = T.acl_nwords, nsw = T.acl_nsw;
+                uint32_t hit = 0xFFFFFFFFu;
+                for (uint32_t sw = 0; sw < nsw && hit == 0xFFFFFFFFu; ++sw) {
+                    uint32_t cand = __ldg(T.acl_basesum + (v6 ? nsw : 0) + sw);
+                    for (uint32_t p = 0; p < npos && cand; ++p) {
+                        const uint32_t kb = pos[p];
+                        const uint32_t val = (q[(kb >> 2) * 32] >> (24 - 8 * (kb & 3))) & 0xFFu;
+                        cand &= __ldg(T.acl_sum + ((size_t)slot[p] * 256 + val) * nsw + sw);
                     }
-                    uint32_t any = __ballot_sync(0xFFFFFFFFu, acc != 0);
-                    if (any) {
-                        int src = __ffs(any) - 1;
-                        uint32_t word = __shfl_sync(0xFFFFFFFFu, acc, src);
-                        best = (wbase + src) * 32 + (__ffs(word) - 1);
+                    while (cand) {
+                        const uint32_t wi = sw * 32 + (__ffs(cand) - 1);
+                        cand &= cand - 1;
+                        uint32_t acc = __ldg(T.acl_base + (v6 ? nw : 0) + wi);
+                        for (uint32_t p = 0; p < npos && acc; ++p) {
+                            const uint32_t kb = pos[p];
+                            const uint32_t val = (q[(kb >> 2) * 32] >> (24 - 8 * (kb & 3))) & 0xFFu;
+                            acc &= __ldg(T.acl_bv + ((size_t)slot[p] * 256 + val) * nw + wi);
+                        }
+                        if (acc) {
+                            hit = wi * 32 + (__ffs(acc) - 1);
+                            break;
+                        }
                     }
                 }
-                if (lane == j) my_hit = best;
-            }
-            __syncwarp();
-            if (my_hit != 0xFFFFFFFFu) {
-                uint32_t r = __ldg(T.acl_rule + my_hit);
-                if (COUNTERS) atomicAdd(T.counters + SFC_CNT_RULES0 + (r & 0x0FFFFFFFu), 1ull);
-                if (r & 0x80000000u) {
-                    rhi = res_hi(SFC_ACT_DROP, SFC_NF_NONE, 0);
-                    rlo = res_lo(SFC_STAGE_ACL, r);
-                    done = true;
+                if (hit != 0xFFFFFFFFu) {
+                    const uint32_t r = __ldg(T.acl_rule + hit);
+                    if (COUNTERS) atomicAdd(T.counters + SFC_CNT_RULES0 + (r & 0x0FFFFFFFu), 1ull);
+                    if (r & 0x80000000u) {
+                        rhi = res_hi(SFC_ACT_DROP, SFC_NF_NONE, 0);
+                        rlo = res_lo(SFC_STAGE_ACL, r);
+                        done = true;
+                    }
                 }
             }
         }

@@ -137,7 +137,7 @@ constexpr int kAclMaxPos = 44;
 
 // ---------------------------------------------------------------- image ------------------
 constexpr uint64_t kImageMagic = 0x3130434653303042ull;  // "B00SFC01"
-constexpr uint32_t kImageVersion = 4;
+constexpr uint32_t kImageVersion = 5;
 constexpr size_t kImageAlign = 256;
 
 struct ImageHeader {
@@ -166,6 +166,8 @@ struct ImageHeader {
     uint32_t lpm6_nnodes, lpm6_count;
 
     uint64_t acl_bv_off, acl_base_off, acl_rule_off;
+    uint64_t acl_sum_off, acl_basesum_off;  // aggregated bit vectors: one bit per 32-rule word
+    uint32_t acl_nsw, acl_pad2;             // summary words per (position, value) = ceil(nwords / 32)
     uint32_t acl_nrules, acl_nwords;
     uint32_t acl_npos4, acl_npos6;
     uint8_t acl_pos4[kAclMaxPos];  // key byte index of each active position for v4 packets

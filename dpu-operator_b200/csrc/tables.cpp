@@ -381,8 +381,9 @@ void build_acl(Blob& blob, const std::vector<AclRec>& recs, ImageHeader& H) {
     H.acl_nrules = n;
     H.acl_nwords = nwords;
     H.acl_npos4 = H.acl_npos6 = H.acl_nstored = 0;
+    H.acl_nsw = (nwords + 31) / 32;
     if (!n) {
-        H.acl_bv_off = H.acl_base_off = H.acl_rule_off = blob.reserve(16, 0);
+        H.acl_bv_off = H.acl_base_off = H.acl_rule_off = H.acl_sum_off = H.acl_basesum_off = blob.reserve(16, 0);
         return;
     }
     std::vector<uint8_t> val((size_t)n * kAclKeyBytes), mask((size_t)n * kAclKeyBytes);
@@ -451,6 +452,23 @@ void build_acl(Blob& blob, const std::vector<AclRec>& recs, ImageHeader& H) {
             H.acl_pos6[H.acl_npos6] = (uint8_t)p;
             H.acl_slot6[H.acl_npos6++] = (uint8_t)slot_of[p];
         }
+    }
+    // aggregated bit vectors (Baboescu & Varghese): bit w of a summary = "word w of the bitmap is
+    // non-zero".  ANDing summaries gives a superset of the words whose full AND can be non-zero.
+    {
+        const uint32_t nsw = H.acl_nsw;
+        H.acl_sum_off = blob.reserve(std::max<size_t>((size_t)nstored * 256 * nsw * 4, 16), 0);
+        H.acl_basesum_off = blob.reserve((size_t)2 * nsw * 4, 0);
+        const uint32_t* bvp = blob.at<uint32_t>(H.acl_bv_off);
+        uint32_t* sum = blob.at<uint32_t>(H.acl_sum_off);
+        for (size_t row = 0; row < (size_t)nstored * 256; ++row)
+            for (uint32_t w = 0; w < nwords; ++w)
+                if (bvp[row * nwords + w]) sum[row * nsw + (w >> 5)] |= 1u << (w & 31);
+        const uint32_t* basep = blob.at<uint32_t>(H.acl_base_off);
+        uint32_t* bs = blob.at<uint32_t>(H.acl_basesum_off);
+        for (int v = 0; v < 2; ++v)
+            for (uint32_t w = 0; w < nwords; ++w)
+                if (basep[(size_t)v * nwords + w]) bs[(size_t)v * nsw + (w >> 5)] |= 1u << (w & 31);
     }
     H.acl_rule_off = blob.reserve((size_t)n * 4, 0);
     uint32_t* ar = blob.at<uint32_t>(H.acl_rule_off);
@@ -556,7 +574,9 @@ const char* validate_image(const uint8_t* img, size_t len) {
     if (ok && H.acl_nrules)
         ok = inside(H.acl_bv_off, (uint64_t)H.acl_nstored * 256 * H.acl_nwords * 4) &&
              inside(H.acl_base_off, (uint64_t)2 * H.acl_nwords * 4) &&
-             inside(H.acl_rule_off, (uint64_t)H.acl_nrules * 4);
+             inside(H.acl_rule_off, (uint64_t)H.acl_nrules * 4) &&
+             inside(H.acl_sum_off, (uint64_t)H.acl_nstored * 256 * H.acl_nsw * 4) &&
+             inside(H.acl_basesum_off, (uint64_t)2 * H.acl_nsw * 4) && H.acl_nsw == (H.acl_nwords + 31) / 32;
     return ok ? nullptr : "image: a section lies outside the buffer or a field is out of range";
 }
 
