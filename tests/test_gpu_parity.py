@@ -326,3 +326,40 @@ def test_vsp_replay_on_the_gpu(torch_cuda):
     wa, wn, wp, ws, _ = sfc.result_fields(want)
     assert np.array_equal(ga, wa) and np.array_equal(gp, wp) and np.array_equal(gs, ws)
     assert (gs == consts.STAGE_L2_EXACT).sum() > 0 and (gs == consts.STAGE_L2_WILD).sum() > 0 and (gs == consts.STAGE_MISS).sum() > 0
+
+
+def test_grpc_vsp_drives_the_gpu_dataplane(torch_cuda, tmp_path):
+    """Row f1 end to end: rules arrive over the reference's gRPC plugin boundary and packets are then
+    classified on the GPU by the dataplane the VSP owns."""
+    import importlib
+    import json
+    import os
+
+    from common import ROOT
+    from packets import SMAC, eth
+
+    vs = importlib.import_module("dpu-operator_b200.vsp_server")
+    G = json.load(open(os.path.join(ROOT, "tests", "golden", "replay_rules.json")))
+    mac = lambda s: bytes(int(x, 16) for x in s.split(":"))  # noqa: E731
+    addr = f"unix:{tmp_path}/vsp.sock"
+    server, impl = vs.serve(addr, device=0, rpm_port=G["rpm_port"])
+    try:
+        c = vs.VspClient(addr)
+        c.Init(vs.msg("Vendor.InitRequest")(dpu_mode=True))
+        for i, m in enumerate(G["vf_macs"]):
+            req = vs.msg(f"{vs.OPI}.CreateBridgePortRequest")()
+            req.bridge_port.name, req.bridge_port.spec.mac_address = f"host0-{i}", mac(m)
+            c.CreateBridgePort(req)
+        c.CreateNetworkFunction(vs.msg("Vendor.NFRequest")(input=G["nf_macs"][0], output=G["nf_macs"][1]))
+        dp = impl.vsp.dataplane
+        vf0, inp, out, rpm = (dp.port_lookup(n) for n in ("vf0-1", "dp_interface0", "dp_interface1", "rpm0"))
+        m0, ext = mac(G["vf_macs"][0]), bytes.fromhex("0200000000fe")
+        hops = [(ext, vf0, inp), (m0, inp, vf0), (m0, out, out), (ext, out, rpm), (m0, rpm, out), (ext, inp, None)]
+        hdr = np.frombuffer(b"".join(eth(d, SMAC, 0x0806, bytes(28)) for d, _, _ in hops), np.uint8).reshape(-1, 64)
+        got = classify_dev(torch_cuda, dp, hdr, np.array([h[1] for h in hops], np.uint16))
+        act, _, port, _, _ = sfc.result_fields(got)
+        assert act.tolist() == [consts.ACT_FORWARD] * 5 + [consts.ACT_TO_CP]
+        assert port.tolist()[:5] == [h[2] for h in hops[:5]]
+        c.close()
+    finally:
+        server.stop(0)

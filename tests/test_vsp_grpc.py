@@ -1,0 +1,86 @@
+"""The gRPC front door: a client doing what the daemon's GrpcPlugin does
+(internal/daemon/plugin/vendorplugin.go:183-265) against the B200 VSP on a unix socket — the object
+sequence of the reference's hostsidemanager_test.go / dpusidemanager flows — must leave the rule set
+of tests/golden/replay_rules.json in the dataplane."""
+import importlib
+import json
+import os
+
+import grpc
+import pytest
+
+from common import ROOT, sfc
+
+vs = importlib.import_module("dpu-operator_b200.vsp_server")
+G = json.load(open(os.path.join(ROOT, "tests", "golden", "replay_rules.json")))
+mac = lambda s: bytes(int(x, 16) for x in s.split(":"))  # noqa: E731
+
+
+@pytest.fixture()
+def vsp(tmp_path):
+    addr = f"unix:{tmp_path}/vendor-plugin.sock"
+    server, impl = vs.serve(addr, device=-1, rpm_port=G["rpm_port"])  # offline dataplane: rule staging only
+    client = vs.VspClient(addr)
+    yield client, impl
+    client.close()
+    server.stop(0)
+
+
+def bridge_port_request(pf, vf, mac_str):
+    # HostSideManager.CreateBridgePort (internal/daemon/hostsidemanager.go:48-74)
+    req = vs.msg(f"{vs.OPI}.CreateBridgePortRequest")()
+    req.bridge_port.name = f"host{pf}-{vf}"
+    req.bridge_port.spec.ptype = 1  # ACCESS
+    req.bridge_port.spec.mac_address = mac(mac_str)
+    req.bridge_port.spec.logical_bridges.append(str(vf + 2))
+    return req
+
+
+def test_daemon_call_sequence_programs_the_26_rules(vsp):
+    client, impl = vsp
+    ipport = client.Init(vs.msg("Vendor.InitRequest")(dpu_mode=True, dpu_identifier="b200-0"))
+    assert (ipport.ip, ipport.port) == ("fe80::1", 8085)
+    devs = client.GetDevices(vs.msg("Vendor.Empty")())
+    assert sorted(devs.devices) == ["nf_interface0", "nf_interface1"] and devs.devices["nf_interface0"].health == "Healthy"
+    for i, m in enumerate(G["vf_macs"]):  # one CNI ADD on the host => exactly one CreateBridgePort (hostsidemanager_test.go:256-261)
+        bp = client.CreateBridgePort(bridge_port_request(0, i, m))
+        assert bp.name == f"bridge_port/host0-{i}" and bp.spec.mac_address == mac(m) and list(bp.spec.logical_bridges) == [str(i + 2)]
+    client.CreateNetworkFunction(vs.msg("Vendor.NFRequest")(input=G["nf_macs"][0], output=G["nf_macs"][1]))
+    assert impl.vsp.flow_dump() == G["rules_ports_then_nf"]
+    client.DeleteBridgePort(vs.msg(f"{vs.OPI}.DeleteBridgePortRequest")(name=G["deleted_bridge_port"]))
+    assert impl.vsp.flow_dump() == G["rules_after_delete_host0_3"]
+    client.DeleteNetworkFunction(vs.msg("Vendor.NFRequest")(input=G["nf_macs"][0], output=G["nf_macs"][1]))
+    assert impl.vsp.flow_dump() == []
+
+
+def test_errors_come_back_as_grpc_status_with_the_reference_text(vsp):
+    client, _ = vsp
+    with pytest.raises(grpc.RpcError) as e:
+        client.GetDevices(vs.msg("Vendor.Empty")())  # before Init: "device Store is empty" (marvell/main.go:625-627)
+    assert e.value.code() == grpc.StatusCode.INTERNAL and "device Store is empty" in e.value.details()
+    client.Init(vs.msg("Vendor.InitRequest")(dpu_mode=True))
+    with pytest.raises(grpc.RpcError) as e:
+        client.SetNumVfs(vs.msg("Vendor.VfCount")(vf_cnt=8))
+    assert "not supported in DPU Mode" in e.value.details()
+    req = bridge_port_request(0, 0, G["vf_macs"][0])
+    req.bridge_port.name = "eth0"
+    with pytest.raises(grpc.RpcError) as e:
+        client.CreateBridgePort(req)
+    assert e.value.code() == grpc.StatusCode.INTERNAL and "no VFId Match Found" in e.value.details()
+
+
+def test_host_mode(vsp):
+    client, impl = vsp
+    ipport = client.Init(vs.msg("Vendor.InitRequest")(dpu_mode=False))
+    assert ipport.ip == "fe80::2"
+    assert client.SetNumVfs(vs.msg("Vendor.VfCount")(vf_cnt=8)).vf_cnt == 8  # dpudevicehandler.go:89
+    assert len(client.GetDevices(vs.msg("Vendor.Empty")()).devices) == 8
+
+
+def test_wire_format_matches_the_reference_field_numbers():
+    # NFRequest{1 input, 2 output} (dpu-api/api.proto:26-29); BridgePortSpec{1 mac bytes, 2 ptype, 3 logical_bridges}
+    assert vs.msg("Vendor.NFRequest")(input="a", output="b").SerializeToString() == b"\n\x01a\x12\x01b"
+    spec = vs.msg(f"{vs.OPI}.BridgePortSpec")(mac_address=b"\x00\x11\x22\x33\x44\x55", ptype=1)
+    spec.logical_bridges.append("7")
+    assert spec.SerializeToString() == b"\n\x06\x00\x11\x22\x33\x44\x55\x10\x01\x1a\x017"
+    assert vs.msg("Vendor.IpPort")(ip="x", port=8085).SerializeToString() == b"\n\x01x\x10\x95?"
