@@ -21,7 +21,7 @@
 using namespace sfc;
 
 namespace {
-constexpr int kTile = 128;
+constexpr int kTile = 256;
 constexpr int kStages = 2;
 constexpr int kTicketRing = 32;      // a launch uses slot seq % 32; slots are 32 bytes apart and self-resetting
 constexpr int kTicketStride = 8;     // u32 words per slot: {draw counter, finished producers, pad}
@@ -47,6 +47,7 @@ struct sfc_handle {
     EncodeTiledFn encode = nullptr;
     int ctas_per_sm[16] = {0};
     int tune_tile = 0, tune_stages = 0;  // SFC_TUNE=tile,stages (experiments)
+    int tune_ctas = 0, tune_carveout = -1;  // cap on resident CTAs per SM / shared-memory carveout percent
     uint32_t flow_first[2] = {0, 0};
     int probe_mode = -1;  // option "flow_probe_mode": -1 auto, else kProbe* bits
     uint32_t* d_tickets = nullptr;  // ring of kTicketRing tile-ticket counters (scratch of the classify kernel)
@@ -175,9 +176,12 @@ int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_
     constexpr int smem = SmemLayout<TILE, STAGES, A>::kBytes;
     if (!h->ctas_per_sm[slot]) {
         CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        if (h->tune_carveout >= 0)
+            CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, h->tune_carveout));
         int per = 0;
         CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, kern, TILE + 32, smem));
         if (per < 1) return fail(h, -EIO, "classify kernel does not fit on an SM");
+        if (h->tune_ctas > 0 && per > h->tune_ctas) per = h->tune_ctas;
         h->ctas_per_sm[slot] = per;
     }
     CUtensorMap map;
@@ -190,7 +194,13 @@ int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(h, -EIO, "cuTensorMapEncodeTiled failed (%d)", (int)r);
     uint64_t n_tiles = (n + TILE - 1) / TILE;
-    uint64_t grid = std::min<uint64_t>(n_tiles, (uint64_t)h->sm_count * h->ctas_per_sm[slot]);
+    // Grid policy (profiles/r01_tuning.md): a launch that runs alone wants every resident CTA it can
+    // get; launches that overlap (SFC_F_OVERLAP) do better with ONE CTA per SM each, because the SM's
+    // remaining room is what lets the next launches become resident early — several small grids in
+    // flight beat one full grid that the next launch has to wait behind (12.3 vs 14.5 us per step).
+    int per_sm = h->ctas_per_sm[slot];
+    if ((flags & SFC_F_OVERLAP) && h->tune_ctas == 0) per_sm = 1;
+    uint64_t grid = std::min<uint64_t>(n_tiles, (uint64_t)h->sm_count * per_sm);
     uint32_t* ticket = h->d_tickets + (h->launches % kTicketRing) * kTicketStride;
     uint32_t overlap = (flags & SFC_F_OVERLAP) ? 1u : 0u;
     cudaLaunchConfig_t cfg = {};
@@ -344,6 +354,11 @@ int sfc_set_option(sfc_handle* h, const char* name, long value) {
     }
     if (!strcmp(name, "tune_stages")) {
         h->tune_stages = (int)value;
+        return 0;
+    }
+    if (!strcmp(name, "tune_ctas") || !strcmp(name, "tune_carveout")) {
+        (name[5] == 'c' && name[6] == 't' ? h->tune_ctas : h->tune_carveout) = (int)value;
+        for (int& c : h->ctas_per_sm) c = 0;  // re-derive occupancy on the next launch
         return 0;
     }
     return fail(h, -ENOENT, "unknown option '%s'", name);

@@ -71,6 +71,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "r"(parity)
         : "memory");
 }
+// same wait, for the producer lane: it only needs to wake up once per tile, so let the hardware park
+// it for a while between polls instead of burning issue slots the consumer warps could use
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+#ifndef SFC_PRODUCER_HINT_NS
+#define SFC_PRODUCER_HINT_NS 2000
+#endif
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAITR_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+        "@p bra DONER_%=;\n\t"
+        "bra WAITR_%=;\n\t"
+        "DONER_%=:\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity), "r"((uint32_t)SFC_PRODUCER_HINT_NS)
+        : "memory");
+}
 __device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar,
                                               uint64_t policy) {
     asm volatile(
@@ -264,7 +280,10 @@ struct SmemLayout {
 };
 
 template <int TILE, int STAGES, bool COUNTERS, bool ACL>
-__global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
+#ifndef SFC_MINB
+#define SFC_MINB 1
+#endif
+__global__ void __launch_bounds__(TILE + 32, SFC_MINB) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
                                                               const uint16_t* __restrict__ in_port,
                                                               uint64_t* __restrict__ result, uint32_t n,
                                                               uint32_t n_tiles, uint32_t* ticket,
@@ -310,7 +329,7 @@ __global__ void __launch_bounds__(TILE + 32) classify_kernel(const __grid_consta
                 const bool have = tile < n_tiles;
                 uint32_t next = 0;
                 if (have) next = gridDim.x + atomicAdd(ticket, 1u);
-                if (use > 0) mbar_wait(empty + s, (use - 1) & 1);
+                if (use > 0) mbar_wait_relaxed(empty + s, (use - 1) & 1);
                 tile_of[s] = have ? tile : 0xFFFFFFFFu;
                 if (!have) {
                     mbar_arrive(full + s);  // end marker: no bytes will follow

@@ -254,7 +254,9 @@ int sfc_table_import_device(sfc_handle* h, const void* dptr, size_t len, void* c
 /* SFC_F_OVERLAP: the caller promises that this launch and the classify launch submitted just
  * before it on the same stream touch different result buffers and do not depend on one another.
  * The library then lets the new launch start while the previous one is still draining
- * (programmatic dependent launch); stream order towards every later operation is kept. */
+ * (programmatic dependent launch); stream order towards every later operation is kept.
+ * Meant for a STREAM of launches: each one uses a small grid so that several are resident at
+ * once; a single isolated launch is faster without the flag. */
 #define SFC_F_OVERLAP 2u
 
 /* Classify n packets.  hdr (n x 64 B, 16-byte aligned), in_port (n x u16) and result (n x u64)

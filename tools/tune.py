@@ -51,6 +51,8 @@ for mode in sys.argv[1:] or ["empty", "cfg2"]:
     dp.set_option("flow_probe_mode", pm)
     for tile, stages in [tuple(map(int, v.split("x"))) for v in os.environ.get("SFC_VARIANTS", "0x0,128x2,128x3,256x2,256x3,512x2").split(",")]:
         dp.set_option("tune_tile", tile); dp.set_option("tune_stages", stages)
+        dp.set_option("tune_carveout", int(os.environ.get("SFC_CARVEOUT", "-1")))
+        dp.set_option("tune_ctas", int(os.environ.get("SFC_CTAS", "0")))
         def run(k):
             for i in range(k):
                 b = i % POOL
