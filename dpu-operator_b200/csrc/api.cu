@@ -127,20 +127,13 @@ void fill_tables(DevTables& T, const ImageHeader& H, const uint8_t* b, unsigned 
     T.lpm6_nodes = (const uint32_t*)(b + H.lpm6_nodes_off);
     T.lpm6_nh = (const LpmRes*)(b + H.lpm6_nh_off);
     T.lpm6_count = H.lpm6_count;
-    T.acl_bv = (const uint32_t*)(b + H.acl_bv_off);
-    T.acl_base = (const uint32_t*)(b + H.acl_base_off);
-    T.acl_rule = (const uint32_t*)(b + H.acl_rule_off);
-    T.acl_sum = (const uint32_t*)(b + H.acl_sum_off);
-    T.acl_basesum = (const uint32_t*)(b + H.acl_basesum_off);
-    T.acl_nsw = H.acl_nsw;
+    T.acl_nodes = (const unsigned long long*)(b + H.acl_nodes_off);
+    T.acl_leaves = (const uint16_t*)(b + H.acl_leaf_off);
+    T.acl_rules = (const uint32_t*)(b + H.acl_rule_off);
+    T.acl_res = (const uint32_t*)(b + H.acl_res_off);
     T.acl_nrules = H.acl_nrules;
-    T.acl_nwords = H.acl_nwords;
-    T.acl_npos4 = H.acl_npos4;
-    T.acl_npos6 = H.acl_npos6;
-    memcpy(T.acl_pos4, H.acl_pos4, kAclMaxPos);
-    memcpy(T.acl_pos6, H.acl_pos6, kAclMaxPos);
-    memcpy(T.acl_slot4, H.acl_slot4, kAclMaxPos);
-    memcpy(T.acl_slot6, H.acl_slot6, kAclMaxPos);
+    T.acl_ntrees = H.acl_ntrees;
+    memcpy(T.acl_roots, H.acl_roots, sizeof(T.acl_roots));
     T.counters = counters;
 }
 
@@ -263,7 +256,7 @@ __global__ void gen_kernel(sfc_gen_spec spec, uint64_t first, uint64_t n, uint8_
 // =================================================================== life cycle ==========
 extern "C" {
 
-const char* sfc_version(void) { return "b200sfc 0.2 (image v5)"; }
+const char* sfc_version(void) { return "b200sfc 0.4 (image v7)"; }
 
 int sfc_create(int device_ordinal, sfc_handle** out) {
     if (!out) return -EINVAL;

@@ -38,13 +38,12 @@ struct DevTables {
     const uint32_t* lpm6_nodes;
     const LpmRes* lpm6_nh;
     uint32_t lpm6_count;
-    const uint32_t* acl_bv;
-    const uint32_t* acl_base;  // [2][nwords]
-    const uint32_t* acl_rule;
-    const uint32_t* acl_sum;      // [stored position][byte value][nsw]
-    const uint32_t* acl_basesum;  // [2][nsw]
-    uint32_t acl_nrules, acl_nwords, acl_npos4, acl_npos6, acl_nsw;
-    uint8_t acl_pos4[kAclMaxPos], acl_pos6[kAclMaxPos], acl_slot4[kAclMaxPos], acl_slot6[kAclMaxPos];
+    const unsigned long long* acl_nodes;  // kAclNodeEntries per node
+    const uint16_t* acl_leaves;           // count, then rank | need flags, ranks ascending
+    const uint32_t* acl_rules;            // kAclRuleWords per rank: groups G0, G1, G2
+    const uint32_t* acl_res;              // per rank: rule id | deny << 31
+    uint32_t acl_nrules, acl_ntrees;
+    unsigned long long acl_roots[kAclMaxTrees];
     unsigned long long* counters;
 };
 
@@ -393,12 +392,10 @@ __global__ void __launch_bounds__(TILE + 32, SFC_MINB) classify_kernel(const __g
         uint32_t rhi = kResMissHi, rlo = kResMissLo;
         bool done = !live;  // lanes past the end of the batch hold zero-filled records
 
-        // ---- stage 1: ACL — byte-sliced bit vectors with an aggregate level, one packet per thread ----
-        // Rules are sorted by (priority desc, id asc), so the first set bit of the AND over the packet's
-        // key bytes is the winner.  The 32-bit summaries (one bit per 32-rule word, L1-resident) are
-        // ANDed first; only words whose summary survives are ANDed in full, in order, until one is
-        // non-zero.  Exact for arbitrary ternary masks; the key words sit in shared memory because the
-        // active byte positions are table data (dynamic indexing).
+        // ---- stage 1: ACL — bit-selecting decision trees, one packet per thread ----
+        // Each tree narrows the candidates to a short leaf list in rank order; the first rule of a leaf
+        // that matches all 11 key words under its mask wins, and the best rank over the trees is the
+        // verdict.  The key words sit in shared memory because the tested bit positions are table data.
         if (ACL) {
             uint32_t* q = aclq + (tid >> 5) * (kAclKeyWords * 32) + lane;
             q[0 * 32] = (port << 16) | (k.meta >> 8);
@@ -410,36 +407,48 @@ __global__ void __launch_bounds__(TILE + 32, SFC_MINB) classify_kernel(const __g
                 q[(7 + i) * 32] = k.dip[i];
             }
             if (live && is_ip) {
-                const bool v6 = k.ip_ver == 6u;
-                const uint8_t* pos = v6 ? T.acl_pos6 : T.acl_pos4;
-                const uint8_t* slot = v6 ? T.acl_slot6 : T.acl_slot4;
-                const uint32_t npos = v6 ? T.acl_npos6 : T.acl_npos4;
-                const uint32_t nw = T.acl_nwords, nsw = T.acl_nsw;
-                uint32_t hit = 0xFFFFFFFFu;
-                for (uint32_t sw = 0; sw < nsw && hit == 0xFFFFFFFFu; ++sw) {
-                    uint32_t cand = __ldg(T.acl_basesum + (v6 ? nsw : 0) + sw);
-                    for (uint32_t p = 0; p < npos && cand; ++p) {
-                        const uint32_t kb = pos[p];
-                        const uint32_t val = (q[(kb >> 2) * 32] >> (24 - 8 * (kb & 3))) & 0xFFu;
-                        cand &= __ldg(T.acl_sum + ((size_t)slot[p] * 256 + val) * nsw + sw);
-                    }
-                    while (cand) {
-                        const uint32_t wi = sw * 32 + (__ffs(cand) - 1);
-                        cand &= cand - 1;
-                        uint32_t acc = __ldg(T.acl_base + (v6 ? nw : 0) + wi);
-                        for (uint32_t p = 0; p < npos && acc; ++p) {
-                            const uint32_t kb = pos[p];
-                            const uint32_t val = (q[(kb >> 2) * 32] >> (24 - 8 * (kb & 3))) & 0xFFu;
-                            acc &= __ldg(T.acl_bv + ((size_t)slot[p] * 256 + val) * nw + wi);
+                // key words in registers for the rule compares (static indices); q[] only serves bit tests
+                const uint32_t q0 = (port << 16) | (k.meta >> 8);
+                const uint32_t q1 = (k.ip_ver << 24) | ((k.meta & 0xFFu) << 16) | (k.ports >> 16), q2 = k.ports << 16;
+                uint32_t best = 0xFFFFFFFFu;
+                for (uint32_t t = 0; t < T.acl_ntrees; ++t) {
+                    unsigned long long e = T.acl_roots[t];
+                    while (!(e & kAclLeaf)) {
+                        uint32_t idx = 0;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const uint32_t pb = (uint32_t)(e >> (28 + 9 * j)) & kAclNoBit;
+                            if (pb != kAclNoBit) idx = (idx << 1) | ((q[(pb >> 5) * 32] >> (31 - (pb & 31))) & 1u);
                         }
-                        if (acc) {
-                            hit = wi * 32 + (__ffs(acc) - 1);
+                        e = __ldg(T.acl_nodes + (size_t)(e & kAclPtrMask) * kAclNodeEntries + idx);
+                    }
+                    const uint16_t* leaf = T.acl_leaves + (e & kAclPtrMask);
+                    const uint32_t cnt = __ldg(leaf);
+                    for (uint32_t i = 1; i <= cnt; ++i) {
+                        const uint32_t le = __ldg(leaf + i), r = le & kAclRankMask;
+                        if (r >= best) break;  // ranks ascend: nothing better left in this leaf
+                        const uint32_t* rec = T.acl_rules + (size_t)r * kAclRuleWords;
+                        uint32_t g[8];
+                        ldg256(rec, g);  // G0: words {1, 2, 7, 3}
+                        uint32_t d = ((q1 ^ g[0]) & g[4]) | ((q2 ^ g[1]) & g[5]) | ((k.dip[0] ^ g[2]) & g[6]) |
+                                     ((k.sip[0] ^ g[3]) & g[7]);
+                        if (d == 0u && (le & kAclNeedG1)) {
+                            ldg256(rec + 8, g);  // G1: words {0, 8, 9, 10}
+                            d = ((q0 ^ g[0]) & g[4]) | ((k.dip[1] ^ g[1]) & g[5]) | ((k.dip[2] ^ g[2]) & g[6]) |
+                                ((k.dip[3] ^ g[3]) & g[7]);
+                        }
+                        if (d == 0u && (le & kAclNeedG2)) {
+                            ldg256(rec + 16, g);  // G2: words {4, 5, 6}
+                            d = ((k.sip[1] ^ g[0]) & g[4]) | ((k.sip[2] ^ g[1]) & g[5]) | ((k.sip[3] ^ g[2]) & g[6]);
+                        }
+                        if (d == 0u) {
+                            best = r;
                             break;
                         }
                     }
                 }
-                if (hit != 0xFFFFFFFFu) {
-                    const uint32_t r = __ldg(T.acl_rule + hit);
+                if (best != 0xFFFFFFFFu) {
+                    const uint32_t r = __ldg(T.acl_res + best);
                     if (COUNTERS) atomicAdd(T.counters + SFC_CNT_RULES0 + (r & 0x0FFFFFFFu), 1ull);
                     if (r & 0x80000000u) {
                         rhi = res_hi(SFC_ACT_DROP, SFC_NF_NONE, 0);

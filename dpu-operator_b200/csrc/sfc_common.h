@@ -133,11 +133,27 @@ constexpr uint32_t kLpmChild = 0x80000000u;
 //   Q3..Q6 = sip[0..3] ; Q7..Q10 = dip[0..3]
 constexpr int kAclKeyWords = 11;
 constexpr int kAclKeyBytes = 44;
-constexpr int kAclMaxPos = 44;
+constexpr int kAclKeyBits = 352;
+// Decision-tree node: 16 child entries of 64 bits (one 128-byte line).  An entry carries the child
+// pointer AND the four bit positions the child tests, so a level costs one load:
+//   bits [0:27)  node index, or — if bit 27 (kAclLeaf) is set — offset into the leaf array
+//   bits [28:64) four 9-bit key-bit positions tested by that child (0x1FF = unused), first = MSB
+// Leaf array (u16): count, then entries rank | needG1 << 12 | needG2 << 13, ranks ascending.
+// Rule record (96 B, three 32-byte groups so the common case is ONE sector):
+//   G0 = value, mask of key words {1, 2, 7, 3}   (ip_ver/proto/sport, dport, dst[0], src[0])
+//   G1 = value, mask of key words {0, 8, 9, 10}  (in_port/vlan, dst[1..3])
+//   G2 = value of words {4, 5, 6}, pad, mask of words {4, 5, 6}, pad   (src[1..3])
+constexpr int kAclNodeEntries = 16;
+constexpr int kAclRuleWords = 24;
+constexpr int kAclMaxTrees = 8;
+constexpr uint64_t kAclLeaf = 1ull << 27;
+constexpr uint64_t kAclPtrMask = (1ull << 27) - 1;
+constexpr uint32_t kAclNoBit = 0x1FFu;
+constexpr uint16_t kAclNeedG1 = 1u << 12, kAclNeedG2 = 1u << 13, kAclRankMask = 0x0FFFu;
 
 // ---------------------------------------------------------------- image ------------------
 constexpr uint64_t kImageMagic = 0x3130434653303042ull;  // "B00SFC01"
-constexpr uint32_t kImageVersion = 5;
+constexpr uint32_t kImageVersion = 7;
 constexpr size_t kImageAlign = 256;
 
 struct ImageHeader {
@@ -165,16 +181,10 @@ struct ImageHeader {
     uint64_t lpm6_root_off, lpm6_nodes_off, lpm6_nh_off;
     uint32_t lpm6_nnodes, lpm6_count;
 
-    uint64_t acl_bv_off, acl_base_off, acl_rule_off;
-    uint64_t acl_sum_off, acl_basesum_off;  // aggregated bit vectors: one bit per 32-rule word
-    uint32_t acl_nsw, acl_pad2;             // summary words per (position, value) = ceil(nwords / 32)
-    uint32_t acl_nrules, acl_nwords;
-    uint32_t acl_npos4, acl_npos6;
-    uint8_t acl_pos4[kAclMaxPos];  // key byte index of each active position for v4 packets
-    uint8_t acl_pos6[kAclMaxPos];
-    uint8_t acl_slot4[kAclMaxPos];  // which stored position table (0..acl_nstored) it uses
-    uint8_t acl_slot6[kAclMaxPos];
-    uint32_t acl_nstored, acl_pad;
+    // ACL: a forest of bit-selecting decision trees over the 352-bit key, leaves scanned in rank order
+    uint64_t acl_nodes_off, acl_leaf_off, acl_rule_off, acl_res_off;
+    uint32_t acl_nrules, acl_nnodes, acl_nleafwords, acl_ntrees;
+    uint64_t acl_roots[kAclMaxTrees];  // node entries (see kAclLeaf)
 };
 static_assert(sizeof(ImageHeader) <= 512, "image header grew past its reserved 512 bytes");
 constexpr size_t kImageHeaderBytes = 512;

@@ -2,6 +2,7 @@
 #include "tables.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace sfc {
@@ -344,30 +345,173 @@ void build_lpm(Blob& blob, const RuleStore& rs, int af, const std::map<RuleStore
 }
 
 // ---- ACL ---------------------------------------------------------------------------------
-void acl_key_bytes(const sfc_acl_rule& r, uint8_t* val, uint8_t* mask) {
-    memset(val, 0, kAclKeyBytes);
-    memset(mask, 0, kAclKeyBytes);
-    auto put16 = [&](int i, uint16_t v, uint16_t m) {
-        val[i] = v >> 8;
-        val[i + 1] = v & 0xFF;
-        mask[i] = m >> 8;
-        mask[i + 1] = m & 0xFF;
+// Bit-selecting decision trees (in the family of HiCuts / EffiCuts / ByteCuts, cutting on single
+// key bits so that ARBITRARY ternary masks stay exact: a rule that does not care about a chosen bit
+// goes to both children).  Rules are ranked by (priority desc, id asc); a leaf lists its candidate
+// rules in rank order and the kernel takes the first that matches in full, so the trees only ever
+// narrow the candidate set — a wrong cut can cost time, never correctness.
+//  * a node tests up to 4 bits (16 children), chosen greedily to minimise the largest child;
+//  * below a rule that matches the whole subspace of a node nothing of lower rank can win: pruned;
+//  * identical sub-problems (same rule list) are built once and shared;
+//  * rules are first split into categories by which fields they leave (almost) open — destination,
+//    source, destination port — one tree per populated category, because a rule that is wild in the
+//    field a tree cuts on would be copied into every branch (the EffiCuts observation).
+void acl_key_words(const sfc_acl_rule& r, uint32_t* val, uint32_t* mask) {
+    uint8_t v[kAclKeyBytes], m[kAclKeyBytes];
+    memset(v, 0, sizeof(v));
+    memset(m, 0, sizeof(m));
+    auto put16 = [&](int i, uint16_t x, uint16_t mm) {
+        v[i] = x >> 8;
+        v[i + 1] = x & 0xFF;
+        m[i] = mm >> 8;
+        m[i + 1] = mm & 0xFF;
     };
     put16(0, r.in_port, r.in_port_mask);
     put16(2, r.vlan, r.vlan_mask);
-    val[4] = r.ip_ver;
-    mask[4] = r.ip_ver ? 0xFF : 0;
-    val[5] = r.proto;
-    mask[5] = r.proto_mask;
+    v[4] = r.ip_ver;
+    m[4] = r.ip_ver ? 0xFF : 0;
+    v[5] = r.proto;
+    m[5] = r.proto_mask;
     put16(6, r.sport, r.sport_mask);
     put16(8, r.dport, r.dport_mask);
     for (int i = 0; i < 16; ++i) {
-        val[12 + i] = r.src[i];
-        mask[12 + i] = r.src_mask[i];
-        val[28 + i] = r.dst[i];
-        mask[28 + i] = r.dst_mask[i];
+        v[12 + i] = r.src[i];
+        m[12 + i] = r.src_mask[i];
+        v[28 + i] = r.dst[i];
+        m[28 + i] = r.dst_mask[i];
+    }
+    for (int w = 0; w < kAclKeyWords; ++w) {
+        mask[w] = be32(m + 4 * w);
+        val[w] = be32(v + 4 * w) & mask[w];
     }
 }
+
+struct AclBuilder {
+    static constexpr int kLeafMax = 8, kMaxDepth = 12, kBitsPerNode = 4;
+    struct R {
+        uint32_t val[kAclKeyWords], mask[kAclKeyWords];
+    };
+    std::vector<R> rules;          // by rank
+    std::vector<uint64_t> nodes;   // kAclNodeEntries per node
+    std::vector<uint16_t> leaves;  // count, entries...
+    std::map<std::vector<uint16_t>, uint64_t> node_memo, leaf_memo;
+    size_t budget_bytes = ~(size_t)0;
+    bool over_budget = false;
+
+    static bool bit(const uint32_t* w, int b) { return (w[b >> 5] >> (31 - (b & 31))) & 1u; }
+    size_t bytes() const { return nodes.size() * 8 + leaves.size() * 2; }
+
+    uint16_t leaf_entry(uint16_t r) const {
+        const uint32_t* m = rules[r].mask;
+        uint16_t e = r;
+        if (m[0] | m[8] | m[9] | m[10]) e |= kAclNeedG1;
+        if (m[4] | m[5] | m[6]) e |= kAclNeedG2;
+        return e;
+    }
+    uint64_t make_leaf(const std::vector<uint16_t>& rs) {
+        auto it = leaf_memo.find(rs);
+        if (it != leaf_memo.end()) return it->second;
+        uint64_t off = leaves.size();
+        leaves.push_back((uint16_t)rs.size());
+        for (uint16_t r : rs) leaves.push_back(leaf_entry(r));
+        return leaf_memo[rs] = kAclLeaf | off | (~0ull << 28);
+    }
+
+    uint64_t build(std::vector<uint16_t> rs, const uint32_t* fixed, int depth) {
+        // prune everything ranked below the first rule that covers this node's whole subspace
+        for (size_t i = 0; i < rs.size(); ++i) {
+            bool covered = true;
+            for (int w = 0; w < kAclKeyWords && covered; ++w) covered = (rules[rs[i]].mask[w] & ~fixed[w]) == 0;
+            if (covered) {
+                rs.resize(i + 1);
+                break;
+            }
+        }
+        if ((int)rs.size() <= kLeafMax || depth >= kMaxDepth || over_budget) return make_leaf(rs);
+        // Sub-problems are shared when the rule list AND the already-decided bits that any of these
+        // rules cares about are the same: the "covers the whole subspace" pruning further down
+        // depends on exactly that, so a subtree must not be reused under different decided bits.
+        std::vector<uint16_t> memo_key = rs;
+        {
+            uint32_t care[kAclKeyWords] = {0};
+            for (uint16_t r : rs)
+                for (int w = 0; w < kAclKeyWords; ++w) care[w] |= rules[r].mask[w];
+            for (int w = 0; w < kAclKeyWords; ++w) {
+                uint32_t f = fixed[w] & care[w];
+                memo_key.push_back((uint16_t)f);
+                memo_key.push_back((uint16_t)(f >> 16));
+            }
+        }
+        auto memo = node_memo.find(memo_key);
+        if (memo != node_memo.end()) return memo->second;
+
+        std::vector<std::vector<uint16_t>> cells(1, rs);
+        int chosen[kBitsPerNode], nchosen = 0;
+        std::vector<uint32_t> n0(kAclKeyBits), n1(kAclKeyBits), worst(kAclKeyBits);
+        std::vector<uint8_t> progress(kAclKeyBits);
+        for (int j = 0; j < kBitsPerNode; ++j) {
+            std::fill(worst.begin(), worst.end(), 0u);
+            std::fill(progress.begin(), progress.end(), 0);
+            for (auto& c : cells) {
+                if (c.empty()) continue;
+                std::fill(n0.begin(), n0.end(), 0u);
+                std::fill(n1.begin(), n1.end(), 0u);
+                for (uint16_t r : c)
+                    for (int w = 0; w < kAclKeyWords; ++w)
+                        for (uint32_t m = rules[r].mask[w]; m; m &= m - 1) {
+                            int bpos = w * 32 + __builtin_clz(m & (~m + 1));  // lowest set bit of m, as an MSB-first position
+                            ((rules[r].val[w] >> (31 - (bpos & 31))) & 1u ? n1 : n0)[bpos]++;
+                        }
+                for (int b = 0; b < kAclKeyBits; ++b) {
+                    uint32_t nw = (uint32_t)c.size() - n0[b] - n1[b];
+                    uint32_t cost = std::max(n0[b], n1[b]) + nw;  // size of the larger child
+                    if (cost < c.size()) progress[b] = 1;
+                    worst[b] = std::max(worst[b], cost);
+                }
+            }
+            int best = -1;
+            for (int b = 0; b < kAclKeyBits; ++b) {
+                if (!progress[b] || bit(fixed, b)) continue;
+                bool used = false;
+                for (int q = 0; q < nchosen; ++q) used = used || chosen[q] == b;
+                if (!used && (best < 0 || worst[b] < worst[best])) best = b;
+            }
+            if (best < 0) break;
+            chosen[nchosen++] = best;
+            std::vector<std::vector<uint16_t>> next;
+            next.reserve(cells.size() * 2);
+            for (auto& c : cells) {
+                std::vector<uint16_t> c0, c1;
+                for (uint16_t r : c) {
+                    bool cares = bit(rules[r].mask, best), one = bit(rules[r].val, best);
+                    if (!cares || !one) c0.push_back(r);
+                    if (!cares || one) c1.push_back(r);
+                }
+                next.push_back(std::move(c0));
+                next.push_back(std::move(c1));
+            }
+            cells.swap(next);
+        }
+        if (!nchosen) return make_leaf(rs);
+
+        uint64_t me = nodes.size() / kAclNodeEntries;
+        nodes.resize(nodes.size() + kAclNodeEntries, make_leaf({}));
+        if (bytes() > budget_bytes) over_budget = true;
+        uint64_t entry = me;
+        for (int q = 0; q < kBitsPerNode; ++q)
+            entry |= (uint64_t)(q < nchosen ? (uint32_t)chosen[q] : kAclNoBit) << (28 + 9 * q);
+        node_memo[memo_key] = entry;
+        uint32_t f[kAclKeyWords];
+        memcpy(f, fixed, sizeof(f));
+        for (int q = 0; q < nchosen; ++q) f[chosen[q] >> 5] |= 1u << (31 - (chosen[q] & 31));
+        // the first chosen bit is the most significant bit of the child index; unused positions add nothing
+        for (int idx = 0; idx < (1 << nchosen); ++idx) {
+            uint64_t child = build(cells[idx], f, depth + 1);
+            nodes[(size_t)me * kAclNodeEntries + idx] = child;
+        }
+        return entry;
+    }
+};
 
 void build_acl(Blob& blob, const std::vector<AclRec>& recs, ImageHeader& H) {
     std::vector<const AclRec*> sorted;
@@ -377,103 +521,79 @@ void build_acl(Blob& blob, const std::vector<AclRec>& recs, ImageHeader& H) {
         return a->id < b->id;
     });
     uint32_t n = (uint32_t)sorted.size();
-    uint32_t nwords = (n + 31) / 32;
     H.acl_nrules = n;
-    H.acl_nwords = nwords;
-    H.acl_npos4 = H.acl_npos6 = H.acl_nstored = 0;
-    H.acl_nsw = (nwords + 31) / 32;
+    H.acl_ntrees = 0;
     if (!n) {
-        H.acl_bv_off = H.acl_base_off = H.acl_rule_off = H.acl_sum_off = H.acl_basesum_off = blob.reserve(16, 0);
+        H.acl_nodes_off = H.acl_leaf_off = H.acl_rule_off = H.acl_res_off = blob.reserve(32, 0);
+        H.acl_nnodes = H.acl_nleafwords = 0;
         return;
     }
-    std::vector<uint8_t> val((size_t)n * kAclKeyBytes), mask((size_t)n * kAclKeyBytes);
-    for (uint32_t i = 0; i < n; ++i)
-        acl_key_bytes(sorted[i]->r, &val[(size_t)i * kAclKeyBytes], &mask[(size_t)i * kAclKeyBytes]);
-    bool active[kAclKeyBytes];
-    for (int p = 0; p < kAclKeyBytes; ++p) {
-        active[p] = false;
-        for (uint32_t i = 0; i < n; ++i)
-            if (mask[(size_t)i * kAclKeyBytes + p]) active[p] = true;
-    }
-    auto bit = [&](uint32_t i, int p, uint32_t v) {
-        uint8_t m = mask[(size_t)i * kAclKeyBytes + p];
-        return ((v & m) == (val[(size_t)i * kAclKeyBytes + p] & m));
+    std::vector<AclBuilder::R> rules(n);
+    for (uint32_t i = 0; i < n; ++i) acl_key_words(sorted[i]->r, rules[i].val, rules[i].mask);
+    auto popcnt = [](const uint32_t* w, int from, int to) {
+        int c = 0;
+        for (int i = from; i < to; ++i) c += __builtin_popcount(w[i]);
+        return c;
     };
-    // bitmaps folded into the per-version base: positions whose packet byte is a constant
-    auto folded4 = [](int p) { return p == 4 || (p >= 16 && p < 28) || (p >= 32 && p < 44); };
-    auto folded6 = [](int p) { return p == 4; };
-    H.acl_base_off = blob.reserve((size_t)2 * nwords * 4, 0);
-    {
-        uint32_t* b4 = blob.at<uint32_t>(H.acl_base_off);
-        uint32_t* b6 = b4 + nwords;
+    // Try the cheapest lookups first: one tree over all rules, then forests split by which of
+    // (dst, dport, src) a rule leaves open; take the first that fits the memory budget.
+    const int feature_sets[4] = {0, 1, 5, 7};
+    const char* force = getenv("SFC_ACL_FEAT");
+    const char* budget_env = getenv("SFC_ACL_BUDGET_MB");
+    const size_t budget = (budget_env ? (size_t)atoi(budget_env) : 24) << 20;
+    AclBuilder B;
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        const int feat = force ? atoi(force) : feature_sets[attempt];
+        B = AclBuilder();
+        B.rules = rules;
+        B.budget_bytes = (force || attempt == 3) ? ~(size_t)0 : budget;
+        std::vector<std::vector<uint16_t>> cat(8);
         for (uint32_t i = 0; i < n; ++i) {
-            bool m4 = true, m6 = true;
-            for (int p = 0; p < kAclKeyBytes; ++p) {
-                if (folded4(p) && !bit(i, p, p == 4 ? 4u : 0u)) m4 = false;
-                if (folded6(p) && !bit(i, p, 6u)) m6 = false;
-            }
-            if (m4) b4[i >> 5] |= 1u << (i & 31);
-            if (m6) b6[i >> 5] |= 1u << (i & 31);
+            const uint32_t* m = rules[i].mask;
+            int c = ((popcnt(m, 7, 11) < 8 ? 1 : 0) | (popcnt(m, 3, 7) < 8 ? 2 : 0) | (__builtin_popcount(m[2]) < 16 ? 4 : 0)) & feat;
+            cat[c].push_back((uint16_t)i);
         }
-    }
-    // stored position tables
-    int slot_of[kAclKeyBytes];
-    uint32_t nstored = 0;
-    for (int p = 0; p < kAclKeyBytes; ++p) slot_of[p] = (active[p] && p != 4) ? (int)nstored++ : -1;
-    H.acl_nstored = nstored;
-    H.acl_bv_off = blob.reserve(std::max<size_t>((size_t)nstored * 256 * nwords * 4, 16), 0);
-    uint32_t* bv = blob.at<uint32_t>(H.acl_bv_off);
-    for (int p = 0; p < kAclKeyBytes; ++p) {
-        if (slot_of[p] < 0) continue;
-        for (uint32_t v = 0; v < 256; ++v) {
-            uint32_t* row = bv + ((size_t)slot_of[p] * 256 + v) * nwords;
-            for (uint32_t i = 0; i < n; ++i)
-                if (bit(i, p, v)) row[i >> 5] |= 1u << (i & 31);
+        std::vector<uint16_t> misc;  // small categories share one tree
+        std::vector<std::vector<uint16_t>> groups;
+        for (auto& c : cat) {
+            if (c.empty()) continue;
+            if (c.size() < 24) misc.insert(misc.end(), c.begin(), c.end());
+            else groups.push_back(c);
         }
-    }
-    // per-version position lists, most selective (fewest set bits on average) first
-    auto selectivity = [&](int p) {
-        uint64_t ones = 0;
-        const uint32_t* t = bv + (size_t)slot_of[p] * 256 * nwords;
-        for (size_t k = 0; k < (size_t)256 * nwords; ++k) ones += (uint64_t)__builtin_popcount(t[k]);
-        return ones;
-    };
-    std::vector<std::pair<uint64_t, int>> order;
-    for (int p = 0; p < kAclKeyBytes; ++p)
-        if (slot_of[p] >= 0) order.push_back({selectivity(p), p});
-    std::sort(order.begin(), order.end());
-    for (auto& o : order) {
-        int p = o.second;
-        if (!folded4(p)) {
-            H.acl_pos4[H.acl_npos4] = (uint8_t)p;
-            H.acl_slot4[H.acl_npos4++] = (uint8_t)slot_of[p];
+        if (!misc.empty()) {
+            std::sort(misc.begin(), misc.end());
+            groups.push_back(misc);
         }
-        if (!folded6(p)) {
-            H.acl_pos6[H.acl_npos6] = (uint8_t)p;
-            H.acl_slot6[H.acl_npos6++] = (uint8_t)slot_of[p];
+        uint32_t fixed0[kAclKeyWords] = {0};
+        H.acl_ntrees = 0;
+        for (auto& g : groups) H.acl_roots[H.acl_ntrees++] = B.build(g, fixed0, 0);
+        if (!B.over_budget || force) break;
+    }
+    H.acl_nnodes = (uint32_t)(B.nodes.size() / kAclNodeEntries);
+    H.acl_nleafwords = (uint32_t)B.leaves.size();
+    H.acl_nodes_off = blob.reserve(std::max<size_t>(B.nodes.size() * 8, 16), 0);
+    if (!B.nodes.empty()) memcpy(blob.at<uint8_t>(H.acl_nodes_off), B.nodes.data(), B.nodes.size() * 8);
+    H.acl_leaf_off = blob.reserve(std::max<size_t>(B.leaves.size() * 2, 16), 0);
+    memcpy(blob.at<uint8_t>(H.acl_leaf_off), B.leaves.data(), B.leaves.size() * 2);
+    H.acl_rule_off = blob.reserve((size_t)n * kAclRuleWords * 4, 0);
+    H.acl_res_off = blob.reserve((size_t)n * 4, 0);
+    uint32_t* rw = blob.at<uint32_t>(H.acl_rule_off);
+    uint32_t* res = blob.at<uint32_t>(H.acl_res_off);
+    const int g0[4] = {1, 2, 7, 3}, g1[4] = {0, 8, 9, 10}, g2[3] = {4, 5, 6};
+    for (uint32_t i = 0; i < n; ++i) {
+        uint32_t* o = rw + (size_t)i * kAclRuleWords;
+        for (int j = 0; j < 4; ++j) {
+            o[j] = rules[i].val[g0[j]];
+            o[4 + j] = rules[i].mask[g0[j]];
+            o[8 + j] = rules[i].val[g1[j]];
+            o[12 + j] = rules[i].mask[g1[j]];
         }
+        for (int j = 0; j < 3; ++j) {
+            o[16 + j] = rules[i].val[g2[j]];
+            o[20 + j] = rules[i].mask[g2[j]];
+        }
+        res[i] = sorted[i]->id | (sorted[i]->r.verdict == SFC_ACL_DENY ? 0x80000000u : 0u);
     }
-    // aggregated bit vectors (Baboescu & Varghese): bit w of a summary = "word w of the bitmap is
-    // non-zero".  ANDing summaries gives a superset of the words whose full AND can be non-zero.
-    {
-        const uint32_t nsw = H.acl_nsw;
-        H.acl_sum_off = blob.reserve(std::max<size_t>((size_t)nstored * 256 * nsw * 4, 16), 0);
-        H.acl_basesum_off = blob.reserve((size_t)2 * nsw * 4, 0);
-        const uint32_t* bvp = blob.at<uint32_t>(H.acl_bv_off);
-        uint32_t* sum = blob.at<uint32_t>(H.acl_sum_off);
-        for (size_t row = 0; row < (size_t)nstored * 256; ++row)
-            for (uint32_t w = 0; w < nwords; ++w)
-                if (bvp[row * nwords + w]) sum[row * nsw + (w >> 5)] |= 1u << (w & 31);
-        const uint32_t* basep = blob.at<uint32_t>(H.acl_base_off);
-        uint32_t* bs = blob.at<uint32_t>(H.acl_basesum_off);
-        for (int v = 0; v < 2; ++v)
-            for (uint32_t w = 0; w < nwords; ++w)
-                if (basep[(size_t)v * nwords + w]) bs[(size_t)v * nsw + (w >> 5)] |= 1u << (w & 31);
-    }
-    H.acl_rule_off = blob.reserve((size_t)n * 4, 0);
-    uint32_t* ar = blob.at<uint32_t>(H.acl_rule_off);
-    for (uint32_t i = 0; i < n; ++i)
-        ar[i] = sorted[i]->id | (sorted[i]->r.verdict == SFC_ACL_DENY ? 0x80000000u : 0u);
 }
 
 }  // namespace
@@ -569,14 +689,12 @@ const char* validate_image(const uint8_t* img, size_t len) {
               inside(H.lpm6_root_off, 65536 * 4) && inside(H.lpm6_nodes_off, (uint64_t)H.lpm6_nnodes * 1024) &&
               inside(H.lpm4_nh_off, 8) && inside(H.lpm6_nh_off, 8) && H.flow4_nhash >= 1 &&
               H.flow4_nhash <= kMaxHashes && H.flow6_nhash >= 1 && H.flow6_nhash <= kMaxHashes && H.flow4_nbuckets &&
-              H.flow6_nbuckets && H.acl_npos4 <= kAclMaxPos && H.acl_npos6 <= kAclMaxPos &&
-              H.acl_nrules <= SFC_MAX_ACL_RULES;
+              H.flow6_nbuckets && H.acl_nrules <= SFC_MAX_ACL_RULES && H.acl_ntrees <= kAclMaxTrees;
     if (ok && H.acl_nrules)
-        ok = inside(H.acl_bv_off, (uint64_t)H.acl_nstored * 256 * H.acl_nwords * 4) &&
-             inside(H.acl_base_off, (uint64_t)2 * H.acl_nwords * 4) &&
-             inside(H.acl_rule_off, (uint64_t)H.acl_nrules * 4) &&
-             inside(H.acl_sum_off, (uint64_t)H.acl_nstored * 256 * H.acl_nsw * 4) &&
-             inside(H.acl_basesum_off, (uint64_t)2 * H.acl_nsw * 4) && H.acl_nsw == (H.acl_nwords + 31) / 32;
+        ok = inside(H.acl_nodes_off, (uint64_t)H.acl_nnodes * kAclNodeEntries * 8) &&
+             inside(H.acl_leaf_off, (uint64_t)H.acl_nleafwords * 2) &&
+             inside(H.acl_rule_off, (uint64_t)H.acl_nrules * kAclRuleWords * 4) &&
+             inside(H.acl_res_off, (uint64_t)H.acl_nrules * 4);
     return ok ? nullptr : "image: a section lies outside the buffer or a field is out of range";
 }
 

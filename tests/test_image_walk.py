@@ -1,0 +1,190 @@
+"""CPU checks of the table-image BUILDER (no GPU): a small Python walker reads the exported image
+with the documented layout (csrc/sfc_common.h) and follows the same structures the kernel follows —
+the ACL decision forest, the LPM tries and the cuckoo buckets — and its answers must equal the
+oracle's.  The walker lives in the tests on purpose: the library has no CPU lookup path."""
+import struct
+
+import numpy as np
+
+from common import Oracle, Scenario, config3_spec, config4_spec, consts, install_flows, install_lpm_acl, sfc
+
+M64 = (1 << 64) - 1
+GAMMA = 0x9E3779B97F4A7C15
+
+
+def mix64(z):
+    z &= M64
+    z ^= z >> 30
+    z = (z * 0xBF58476D1CE4E5B9) & M64
+    z ^= z >> 27
+    z = (z * 0x94D049BB133111EB) & M64
+    return z ^ (z >> 31)
+
+
+def expand_seed(seed, n):
+    return [((mix64(seed + (i + 1) * GAMMA) >> 16) & 0xFFFFFFFF) | 1 for i in range(n)]
+
+
+class Image:
+    """Field offsets follow struct ImageHeader (version 7)."""
+
+    def __init__(self, img: np.ndarray):
+        self.b = img.tobytes()
+        u = lambda fmt, off: struct.unpack_from("<" + fmt, self.b, off)  # noqa: E731
+        magic, ver, hb, total, epoch = u("QIIQQ", 0)
+        assert magic == 0x3130434653303042 and ver == 7 and hb == 512 and total == len(self.b)
+        o = 32
+        self.f4_off, self.f4_seed, self.f4_nb, self.f4_nh, self.f4_cnt, self.f4_first = u("QQIIII", o); o += 32
+        self.f6_off, self.f6_seed, self.f6_nb, self.f6_nh, self.f6_cnt, self.f6_first = u("QQIIII", o); o += 32
+        self.l2x_off, self.l2x_mask, self.l2x_cnt, self.l2w_off, self.l2w_n, self.l2w_cnt = u("QIIQII", o); o += 32
+        self.lpm4 = u("QQQII", o); o += 32
+        self.lpm6 = u("QQQII", o); o += 32
+        self.acl_nodes_off, self.acl_leaf_off, self.acl_rule_off, self.acl_res_off = u("QQQQ", o); o += 32
+        self.acl_nrules, self.acl_nnodes, self.acl_nleaf, self.acl_ntrees = u("IIII", o); o += 16
+        self.acl_roots = u("8Q", o)
+
+    def u32(self, off, n):
+        return np.frombuffer(self.b, dtype="<u4", count=n, offset=off)
+
+    # ---- ACL forest: returns winning rule word (id | deny<<31) or None ----
+    def acl(self, q, stats=None):  # q: 11 key words
+        LEAF, PTR = 1 << 27, (1 << 27) - 1
+        groups = ((1, 2, 7, 3), (0, 8, 9, 10), (4, 5, 6))
+        best = None
+        for t in range(self.acl_ntrees):
+            e = self.acl_roots[t]
+            while not e & LEAF:
+                idx = 0
+                for j in range(4):
+                    p = (e >> (28 + 9 * j)) & 0x1FF
+                    if p != 0x1FF:
+                        idx = (idx << 1) | ((q[p >> 5] >> (31 - (p & 31))) & 1)
+                e = int(np.frombuffer(self.b, dtype="<u8", count=1, offset=self.acl_nodes_off + ((e & PTR) * 16 + idx) * 8)[0])
+                if stats is not None:
+                    stats["visits"] += 1
+            off = self.acl_leaf_off + (e & PTR) * 2
+            cnt = int(np.frombuffer(self.b, dtype="<u2", offset=off, count=1)[0])
+            for le in np.frombuffer(self.b, dtype="<u2", offset=off + 2, count=cnt):
+                le = int(le)
+                r = le & 0x0FFF
+                if best is not None and r >= best:
+                    break
+                if stats is not None:
+                    stats["compares"] += 1
+                rec = self.u32(self.acl_rule_off + r * 96, 24)
+                ok = all(((q[w] ^ int(rec[j])) & int(rec[4 + j])) == 0 for j, w in enumerate(groups[0]))
+                if ok and le & 0x1000:
+                    ok = all(((q[w] ^ int(rec[8 + j])) & int(rec[12 + j])) == 0 for j, w in enumerate(groups[1]))
+                if ok and le & 0x2000:
+                    ok = all(((q[w] ^ int(rec[16 + j])) & int(rec[20 + j])) == 0 for j, w in enumerate(groups[2]))
+                if ok:
+                    best = r
+                    break
+        return None if best is None else int(self.u32(self.acl_res_off + best * 4, 1)[0])
+
+    def lpm(self, af, addr_words):
+        root_off, nodes_off, nh_off, nnodes, cnt = self.lpm4 if af == 4 else self.lpm6
+        e = int(self.u32(root_off + (addr_words[0] >> 16) * 4, 1)[0])
+        pos = 16
+        while e & 0x80000000 and pos < (32 if af == 4 else 128):
+            byte = (addr_words[pos >> 5] >> (24 - (pos & 31))) & 0xFF
+            e = int(self.u32(nodes_off + ((e & 0x7FFFFFFF) * 256 + byte) * 4, 1)[0])
+            pos += 8
+        if e & 0x80000000 or e == 0:
+            return None
+        hi, lo = self.u32(nh_off + (e - 1) * 8, 2)
+        return (int(hi) << 32) | int(lo)
+
+    def flow4(self, sip, dip, ports, meta20):
+        S = expand_seed(self.f4_seed, 10)
+        P = ((sip ^ S[0]) * (dip ^ S[1])) & M64
+        Q = ((ports ^ S[2]) * (meta20 ^ S[3])) & M64
+        x = (P & 0xFFFFFFFF) ^ (Q >> 32)
+        y = (P >> 32) ^ (Q & 0xFFFFFFFF)
+        for j in range(self.f4_nh):
+            F = ((x ^ S[4 + 2 * j]) * (y ^ S[5 + 2 * j])) & M64
+            h = (F & 0xFFFFFFFF) ^ (F >> 32)
+            b = (h * self.f4_nb) >> 32
+            s = self.u32(self.f4_off + b * 32, 8)
+            if (int(s[0]), int(s[1]), int(s[2]), int(s[3])) == (sip, dip, ports, meta20 | 0x80000000):
+                return (int(s[4]) << 32) | int(s[5]), j
+        return None, None
+
+
+def acl_key(pkt, in_port):
+    p = Oracle.parse(pkt)
+    w = lambda b: int.from_bytes(b, "big")  # noqa: E731
+    q = [(in_port << 16) | p["vlan"], (p["ver"] << 24) | (p["proto"] << 16) | p["sport"], p["dport"] << 16]
+    q += [w(p["src"][i:i + 4]) for i in range(0, 16, 4)] + [w(p["dst"][i:i + 4]) for i in range(0, 16, 4)]
+    return p, q
+
+
+def test_acl_forest_and_lpm_tries_answer_like_the_oracle():
+    sc = Scenario(sfc.Dataplane(-1))
+    spec = config4_spec(n_pfx4=3000, n_pfx6=800, n_acl=400)
+    rules = install_lpm_acl(sc, spec)
+    sc.dp.commit()
+    img = Image(sc.dp.table_export())
+    assert img.acl_nrules == 400 and 1 <= img.acl_ntrees <= 8
+    hdr, ports = sfc.gen_packets_host(spec, 0, 3000)
+    want = sc.orc.classify(hdr, ports)
+    act, _, _, stage, index = sfc.result_fields(want)
+    checked_acl = checked_lpm = 0
+    for i in range(len(ports)):
+        p, q = acl_key(hdr[i], int(ports[i]))
+        if p["ver"] == 0:
+            continue
+        r = img.acl(q)
+        if stage[i] == consts.STAGE_ACL:  # the oracle dropped it: the forest must name the same deny rule
+            assert r is not None and r >> 31 == 1 and (r & 0x0FFFFFFF) == index[i], i
+            checked_acl += 1
+            continue
+        assert r is None or r >> 31 == 0, f"packet {i}: forest says deny, oracle let it pass"
+        dst = [q[7], q[8], q[9], q[10]]
+        got = img.lpm(p["ver"], dst)
+        if stage[i] in (consts.STAGE_LPM4, consts.STAGE_LPM6):
+            assert got == int(want[i]), i
+            checked_lpm += 1
+        else:
+            assert got is None
+    assert checked_acl > 5 and checked_lpm > 1000
+
+
+def test_acl_forest_on_the_handmade_rules():
+    from packets import handmade_cases
+
+    sc = Scenario(sfc.Dataplane(-1))
+    hdr, ports = handmade_cases(sc)
+    sc.dp.commit()
+    img = Image(sc.dp.table_export())
+    want = sc.orc.classify(hdr, ports)
+    stage, index = sfc.result_fields(want)[3:5]
+    for i in range(len(ports)):
+        p, q = acl_key(hdr[i], int(ports[i]))
+        if p["ver"] == 0:
+            continue
+        r = img.acl(q)
+        if stage[i] == consts.STAGE_ACL:
+            assert r is not None and r >> 31 == 1 and (r & 0x0FFFFFFF) == index[i]
+        else:
+            assert r is None or r >> 31 == 0
+
+
+def test_every_ipv4_flow_sits_in_one_of_its_buckets():
+    sc = Scenario(sfc.Dataplane(-1))
+    spec = config3_spec(n_flows=20000, v6_permille=0, n_ports=8)
+    install_flows(sc, spec)
+    sc.dp.commit()
+    img = Image(sc.dp.table_export())
+    assert img.f4_cnt == 20000 and img.f4_nb >= 20000 / 0.45
+    keys, acts = sfc.gen_flows(spec, 0, 20000)
+    first = 0
+    for i in range(0, 20000, 7):
+        k = keys[i]
+        sip, dip = int.from_bytes(bytes(k["src"][:4]), "big"), int.from_bytes(bytes(k["dst"][:4]), "big")
+        res, j = img.flow4(sip, dip, (int(k["sport"]) << 16) | int(k["dport"]), int(k["proto"]) | (int(k["vlan"]) << 8))
+        assert res is not None, f"flow {i} is not where the hash says"
+        assert res & 0x0FFFFFFF == i and (res >> 28) & 0xF == consts.STAGE_FLOW and res >> 56 == int(acts[i]["action"])
+        first += j == 0
+    assert first / len(range(0, 20000, 7)) > 0.6  # most flows answer on the first probe
+    assert abs(img.f4_first / 20000 - first / len(range(0, 20000, 7))) < 0.05  # header statistic is honest

@@ -1,0 +1,33 @@
+"""A few classify launches of one BASELINE config for ncu.  usage: python tools/prof_cfg.py cfg3|cfg5|cfg4 [launches]"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import torch
+from common import Scenario, config3_spec, config4_spec, install_flows, install_lpm_acl, sfc
+
+which = sys.argv[1] if len(sys.argv) > 1 else "cfg3"
+launches = int(sys.argv[2]) if len(sys.argv) > 2 else 6
+dp = sfc.Dataplane(0); sc = Scenario(dp)
+if which == "cfg3":
+    topo = sc.build_chain(8, 4)
+    spec = config3_spec(n_flows=1 << 20, n_ports=topo["n_ports"])
+    install_flows(sc, spec)
+elif which == "cfg4":
+    spec = config4_spec(); install_lpm_acl(sc, spec)
+else:
+    spec = config3_spec(n_flows=1 << 24, n_ports=17)
+    for first in range(0, 1 << 24, 1 << 20):
+        k, a = sfc.gen_flows(spec, first, 1 << 20); dp.flow_add_bulk(k, a)
+dp.commit()
+M = 1 << 20
+st = torch.cuda.current_stream().cuda_stream
+hdr = torch.empty((launches, M, 64), dtype=torch.uint8, device="cuda")
+ports = torch.empty((launches, M), dtype=torch.int16, device="cuda")
+res = torch.zeros((launches, M), dtype=torch.int64, device="cuda")
+for i in range(launches):
+    dp.gen_packets(spec, i * M, M, hdr[i].data_ptr(), ports[i].data_ptr(), st)
+torch.cuda.synchronize()
+for i in range(launches):
+    dp.classify(hdr[i].data_ptr(), ports[i].data_ptr(), res[i].data_ptr(), M, 0, st)
+torch.cuda.synchronize()
+print("done", which, dp.table_size)
