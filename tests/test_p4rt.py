@@ -1,0 +1,108 @@
+"""Row f2: the P4Runtime rule-string importer against fixtures produced by the REFERENCE's own
+p4rt-ctl code (tests/golden/make_p4rt.py), and the mapping of the importable tables onto the
+dataplane checked per packet with the oracle."""
+import importlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from common import ROOT, Oracle, Scenario, consts, sfc
+from packets import SMAC, eth, ipv4, ipv6, ports as l4ports
+
+p4rt = importlib.import_module("dpu-operator_b200.p4rt")
+G = json.load(open(os.path.join(ROOT, "tests", "golden", "p4rt_entries.json")))["entries"]
+C = "linux_networking_control."
+
+
+@pytest.mark.parametrize("g", G, ids=[f"{i}-{g['table'].split('.')[-1]}" for i, g in enumerate(G)])
+def test_entry_equals_the_reference_table_entry(g):
+    e = p4rt.parse_entry(g["table"], g["rule"])
+    assert (e.table_id, e.action_id, e.priority) == (g["table_id"], g["action_id"], g["priority"])
+    assert [dict(id=pid, value=v.hex()) for pid, _, v in e.params] == g["params"]
+    got = []
+    for m in e.match:
+        d = dict(field_id=m.field_id, kind=m.kind, value=m.value.hex())
+        if m.kind == "lpm":
+            d["prefix_len"] = m.prefix_len
+        if m.kind == "ternary":
+            d["mask"] = m.mask.hex()
+        got.append(d)
+    assert got == g["match"]
+    assert e.serialize().hex() == g["wire"], "protobuf bytes differ from the reference's TableEntry"
+
+
+def test_schema_is_the_reference_p4info():
+    s = p4rt.load_schema()
+    assert len(s["tables"]) == 55 and len(s["actions"]) == 81  # 55 tables, 81 actions
+    t = s["tables"][C + "ipv6_table"]
+    assert [(f["name"], f["bitwidth"], f["kind"]) for f in t["match_fields"]] == [("ipv6_table_lpm_root", 32, "exact"), ("ipv6_dst_match", 128, "lpm")]
+    assert all(t["size"] in (1024, 256, 0) or t["size"] > 0 for t in s["tables"].values())
+
+
+def test_errors_follow_p4rt_ctl():
+    with pytest.raises(p4rt.P4Error, match="priority field is needed"):
+        p4rt.parse_entry(C + "tx_source_port", f"vmeta.common.vsi=5/0x7ff,action={C}set_source_port(21)")
+    with pytest.raises(p4rt.P4Error, match="does not fit in 11 bits"):
+        p4rt.parse_entry(C + "tx_acc_vsi", f"vmeta.common.vsi=4096,zero_padding=0,action={C}l2_fwd_and_bypass_bridge(1)")
+    with pytest.raises(p4rt.P4Error, match="unknown table"):
+        p4rt.parse_entry(C + "no_such_table", "a=1,action=b")
+    with pytest.raises(p4rt.P4Error, match="not valid for table"):
+        p4rt.parse_entry(C + "ipv4_table", f"ipv4_table_lpm_root=0,ipv4_dst_match=10.0.0.0/8,action={C}l2_fwd(1)")
+    with pytest.raises(p4rt.P4Error, match="no match field"):
+        p4rt.parse_entry(C + "ipv4_table", f"bogus=0,action={C}ipv4_set_nexthop_id(1)")
+
+
+def test_importer_maps_routes_bridges_and_port_maps_onto_the_dataplane():
+    imp = p4rt.Importer()
+    for g in G:
+        imp.add(g["table"], g["rule"])
+    dp = sfc.Dataplane(-1)
+    for i in range(32):
+        dp.port_add(f"p{i}")  # Intel port numbers are used as port ids one to one
+    done = imp.apply(dp)
+    # 3 IPv4 routes + 1 IPv6 route; next hop 9 drops -> that /32 stays unresolved
+    assert done == dict(lpm=3, l2_exact=4, l2_wildcard=2, unresolved_routes=1, unmapped=7)
+    assert sorted(e.table.split(".")[-1] for e in imp.unmapped) == [
+        "ipsec_spd", "nexthop_table", "tx_acc_vsi", "tx_lag_table", "tx_source_port", "vsi_to_vsi_loopback", "vsi_to_vsi_loopback"]
+    dp.commit()
+    # the same rules into the oracle, by hand
+    orc = Oracle()
+    orc.lpm_add(4, bytes([10, 1, 2, 0]), 24, 21, 0)
+    orc.lpm_add(4, bytes([10, 1, 0, 0]), 16, 25, 1)
+    orc.lpm_add(6, bytes.fromhex("20010db8000100000000000000000000"), 48, 21, 2)
+    rid = 0
+    for mac, port in ((bytes.fromhex("000500000314"), 21), (bytes.fromhex("001122334455"), 25), (bytes.fromhex("0200000000fe"), 0)):
+        for in_port in (0, 21):  # members of bridge 77
+            if in_port != port:
+                orc.l2_add(in_port, port, mac, consts.PRIO_MAC, rid)
+                rid += 1
+    orc.l2_add(21, 25, None, consts.PRIO_WILDCARD, rid)
+    orc.l2_add(22, 26, None, consts.PRIO_WILDCARD, rid + 1)
+    # compare structure of the image-free rule store through the library's own dump: port list + classify on GPU
+    # is covered elsewhere; here the oracle answers for the intended semantics
+    A, other = bytes([192, 0, 2, 1]), bytes.fromhex("0200deadbeef")
+    frames = [
+        (eth(other, SMAC, 0x0800, ipv4(A, bytes([10, 1, 2, 9]), 6, l4ports(1, 2))), 5, 21, consts.STAGE_LPM4),   # /24 -> nh 7 -> port 21
+        (eth(other, SMAC, 0x0800, ipv4(A, bytes([10, 1, 9, 9]), 6, l4ports(1, 2))), 5, 25, consts.STAGE_LPM4),   # /16 -> nh 8 -> port 25
+        (eth(other, SMAC, 0x0800, ipv4(A, bytes([192, 168, 7, 9]), 6, l4ports(1, 2))), 5, 0, consts.STAGE_MISS),  # next hop drops: unresolved
+        (eth(other, SMAC, 0x86DD, ipv6(bytes(16), bytes.fromhex("20010db8000100000000000000000001"), 6, l4ports(1, 2))), 5, 21, consts.STAGE_LPM6),
+        (eth(bytes.fromhex("001122334455"), SMAC, 0x0806, bytes(28)), 0, 25, consts.STAGE_L2_EXACT),   # bridge 77 member 0
+        (eth(bytes.fromhex("001122334455"), SMAC, 0x0806, bytes(28)), 21, 25, consts.STAGE_L2_EXACT),  # MAC rule beats the port map
+        (eth(other, SMAC, 0x0806, bytes(28)), 21, 25, consts.STAGE_L2_WILD),                           # source_port_to_pr_map
+        (eth(other, SMAC, 0x0806, bytes(28)), 22, 26, consts.STAGE_L2_WILD),
+        (eth(other, SMAC, 0x0806, bytes(28)), 7, 0, consts.STAGE_MISS),
+    ]
+    hdr = np.frombuffer(b"".join(f for f, *_ in frames), np.uint8).reshape(-1, 64)
+    res = orc.classify(hdr, np.array([f[1] for f in frames], np.uint16))
+    _, _, port, stage, _ = sfc.result_fields(res)
+    assert port.tolist() == [f[2] for f in frames] and stage.tolist() == [f[3] for f in frames]
+    # and the library staged exactly those rules: its image must answer the same (walker from test_image_walk)
+    from test_image_walk import Image
+
+    img = Image(dp.table_export())
+    assert img.lpm4[4] == 2 and img.lpm6[4] == 1 and img.l2x_cnt == 4 and img.l2w_cnt == 2
+    assert img.lpm(4, [0x0A010209, 0, 0, 0]) & 0xFFFF_0000_0000 == 21 << 32
+    assert img.lpm(4, [0x0A010909, 0, 0, 0]) & 0xFFFF_0000_0000 == 25 << 32
+    assert img.lpm(4, [0xC0A80709, 0, 0, 0]) is None
