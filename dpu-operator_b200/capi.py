@@ -76,6 +76,8 @@ def _load():
         "sfc_acl_del": (C.c_int, [vp, C.c_uint32]),
         "sfc_clear": (C.c_int, [vp]),
         "sfc_commit": (C.c_int, [vp]),
+        "sfc_commit_stream": (C.c_int, [vp, vp]),
+        "sfc_stat": (C.c_long, [vp, C.c_char_p]),
         "sfc_table_size": (C.c_size_t, [vp]),
         "sfc_table_epoch": (C.c_uint64, [vp]),
         "sfc_table_export": (C.c_int, [vp, vp, C.c_size_t]),
@@ -254,6 +256,15 @@ class Dataplane:
     # ---- commit / image ----
     def commit(self):
         self._chk(lib.sfc_commit(self._h))
+
+    def commit_stream(self, stream: int = 0):
+        self._chk(lib.sfc_commit_stream(self._h, stream))
+
+    def stat(self, name: str) -> int:
+        v = lib.sfc_stat(self._h, name.encode())
+        if v < 0:
+            raise SfcError(int(v), f"unknown stat {name!r}")
+        return int(v)
 
     @property
     def table_size(self) -> int:

@@ -58,6 +58,16 @@ struct sfc_handle {
     uint16_t* d_port[2] = {nullptr, nullptr};
     uint64_t* d_res[2] = {nullptr, nullptr};
     float last_kernel_ms = -1.f;
+    // host shadows of the committed flow tables + staging for incremental commits
+    FlowTable shadow4, shadow6;
+    std::vector<uint32_t> shadow4_mem, shadow6_mem;
+    ImageHeader header{};  // header of the committed image (host copy)
+    bool shadow_valid = false;
+    uint8_t* h_patch = nullptr;   // pinned: [indices u32 ...][bucket data ...]
+    uint8_t* d_patch = nullptr;
+    size_t patch_cap = 0;
+    cudaEvent_t patch_done = nullptr;
+    uint64_t n_full_commits = 0, n_incremental_commits = 0, n_patched_buckets = 0;
     // offline handles (device_ordinal -1): rule staging and image building only, no CUDA calls
     std::vector<uint8_t> host_image;
     bool offline() const { return device < 0; }
@@ -238,6 +248,15 @@ int launch_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uin
     return launch_variant<kTile, kStages, false, false>(h, 0, hdr, in_port, result, n, flags, st);
 }
 
+// Incremental commit: write `n` whole buckets (bucket_words u32 each) into a flow table in place.
+// Runs in stream order between classify launches, never concurrently with one on the same stream.
+__global__ void patch_buckets_kernel(uint32_t* table, const uint32_t* idx, const uint32_t* data, uint32_t n,
+                                     uint32_t bucket_words) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t b = t / bucket_words, w = t % bucket_words;
+    if (b < n) table[(size_t)idx[b] * bucket_words + w] = data[(size_t)b * bucket_words + w];
+}
+
 __global__ void gen_kernel(sfc_gen_spec spec, uint64_t first, uint64_t n, uint8_t* hdr, uint16_t* in_port) {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -309,6 +328,9 @@ int sfc_destroy(sfc_handle* h) {
     if (h->d_image) cudaFree(h->d_image);
     if (h->d_counters) cudaFree(h->d_counters);
     if (h->d_tickets) cudaFree(h->d_tickets);
+    if (h->h_patch) cudaFreeHost(h->h_patch);
+    if (h->d_patch) cudaFree(h->d_patch);
+    if (h->patch_done) cudaEventDestroy(h->patch_done);
     for (int i = 0; i < 2; ++i) {
         if (h->d_hdr[i]) cudaFree(h->d_hdr[i]);
         if (h->d_port[i]) cudaFree(h->d_port[i]);
@@ -327,11 +349,13 @@ int sfc_set_option(sfc_handle* h, const char* name, long value) {
     if (!h || !name) return -EINVAL;
     if (!strcmp(name, "flow_load_pct")) {
         if (value < 5 || value > 90) return fail(h, -EINVAL, "flow_load_pct must be 5..90");
+        h->rs.other_dirty = true;
         h->rs.flow_load_pct = (int)value;
         return 0;
     }
     if (!strcmp(name, "flow_hashes")) {
         if (value < 2 || value > kMaxHashes) return fail(h, -EINVAL, "flow_hashes must be 2 or 3");
+        h->rs.other_dirty = true;
         h->rs.flow_hashes = (int)value;
         return 0;
     }
@@ -411,6 +435,7 @@ long sfc_port_list(const sfc_handle* h, char* buf, size_t len) {
 // =================================================================== L2 steering =========
 int sfc_l2_rule_add(sfc_handle* h, uint16_t in_port, uint16_t out_port, const uint8_t* dst_mac, uint32_t* rule_id) {
     if (!h) return -EINVAL;
+    h->rs.other_dirty = true;  // not a flow edit: the next commit rebuilds the image
     if (in_port >= SFC_MAX_PORTS || out_port >= SFC_MAX_PORTS)
         return fail(h, -EINVAL, "sfc_l2_rule_add: port id out of range");
     L2Rule r{};
@@ -436,6 +461,7 @@ int sfc_l2_rule_add(sfc_handle* h, uint16_t in_port, uint16_t out_port, const ui
 
 int sfc_l2_rule_del(sfc_handle* h, uint16_t in_port, const uint8_t* dst_mac) {
     if (!h) return -EINVAL;
+    h->rs.other_dirty = true;  // not a flow edit: the next commit rebuilds the image
     auto& v = h->rs.l2;
     v.erase(std::remove_if(v.begin(), v.end(),
                            [&](const L2Rule& e) {
@@ -449,6 +475,7 @@ int sfc_l2_rule_del(sfc_handle* h, uint16_t in_port, const uint8_t* dst_mac) {
 
 int sfc_chain_set(sfc_handle* h, const uint16_t* nf_in_ports, const uint16_t* nf_out_ports, size_t n_nfs) {
     if (!h) return -EINVAL;
+    h->rs.other_dirty = true;  // not a flow edit: the next commit rebuilds the image
     if (n_nfs > SFC_MAX_NFS) return fail(h, -EINVAL, "sfc_chain_set: at most %u network functions", SFC_MAX_NFS);
     if (n_nfs && (!nf_in_ports || !nf_out_ports)) return fail(h, -EINVAL, "sfc_chain_set: null port array");
     for (size_t i = 0; i < n_nfs; ++i)
@@ -465,7 +492,8 @@ int sfc_flow_add_bulk(sfc_handle* h, const sfc_flow_key* keys, const sfc_flow_ac
     if (!h || (n && (!keys || !acts))) return -EINVAL;
     RuleStore& rs = h->rs;
     if ((uint64_t)rs.next_flow_id + n > SFC_MAX_FLOWS) return fail(h, -ENOSPC, "flow ids exhausted");
-    size_t before = rs.flows.size();
+    size_t before = rs.flows.size(), log_before = rs.flow_log.size();
+    const bool log_it = !rs.other_dirty && rs.flow_log.size() + n <= (1u << 20);
     uint32_t id0 = rs.next_flow_id;
     if (n > 4096) rs.flows.reserve(before + n);
     std::string err;
@@ -480,12 +508,15 @@ int sfc_flow_add_bulk(sfc_handle* h, const sfc_flow_key* keys, const sfc_flow_ac
         if (code) {  // roll the whole batch back
             rs.flows.resize(before);
             rs.flow_index.rebuild(rs.flows, before);
+            rs.flow_log.resize(log_before);
             return fail(h, code, "sfc_flow_add: entry %zu: %s", i, err.c_str());
         }
         f.id = id0 + (uint32_t)i;
         rs.flows.push_back(f);
         rs.flow_index.insert(rs.flows, (uint32_t)(rs.flows.size() - 1));
+        if (log_it) rs.flow_log.push_back(FlowChange{true, f});
     }
+    if (!log_it) rs.other_dirty = true;  // a bulk load this large is cheaper as a rebuild
     rs.next_flow_id = id0 + (uint32_t)n;
     if (first_id) *first_id = id0;
     return 0;
@@ -503,9 +534,8 @@ int sfc_flow_del(sfc_handle* h, const sfc_flow_key* key) {
     if (!flow_from_key(*key, a, f, err)) return fail(h, -EINVAL, "sfc_flow_del: %s", err.c_str());
     int64_t pos = h->rs.flow_index.find(h->rs.flows, f);
     if (pos < 0) return fail(h, -ENOENT, "sfc_flow_del: no such flow");
-    h->rs.flows[pos] = h->rs.flows.back();
-    h->rs.flows.pop_back();
-    h->rs.flow_index.rebuild(h->rs.flows, h->rs.flows.size());
+    if (!h->rs.other_dirty) h->rs.flow_log.push_back(FlowChange{false, h->rs.flows[pos]});
+    h->rs.flow_index.erase(h->rs.flows, (uint32_t)pos);
     return 0;
 }
 
@@ -525,6 +555,7 @@ static int lpm_words(sfc_handle* h, int af, const uint8_t* prefix, int len, uint
 
 int sfc_lpm_add(sfc_handle* h, int af, const uint8_t* prefix, int len, uint16_t out_port, uint32_t* prefix_id) {
     if (!h) return -EINVAL;
+    h->rs.other_dirty = true;  // not a flow edit: the next commit rebuilds the image
     LpmRec r{};
     int rc = lpm_words(h, af, prefix, len, r.w);
     if (rc) return rc;
@@ -548,6 +579,7 @@ int sfc_lpm_add(sfc_handle* h, int af, const uint8_t* prefix, int len, uint16_t 
 
 int sfc_lpm_del(sfc_handle* h, int af, const uint8_t* prefix, int len) {
     if (!h) return -EINVAL;
+    h->rs.other_dirty = true;  // not a flow edit: the next commit rebuilds the image
     uint32_t w[4];
     int rc = lpm_words(h, af, prefix, len, w);
     if (rc) return rc;
@@ -560,6 +592,7 @@ int sfc_lpm_del(sfc_handle* h, int af, const uint8_t* prefix, int len) {
 // =================================================================== ACL =================
 int sfc_acl_add(sfc_handle* h, const sfc_acl_rule* rule, uint32_t* rule_id) {
     if (!h || !rule) return -EINVAL;
+    h->rs.other_dirty = true;
     if (h->rs.acl.size() >= SFC_MAX_ACL_RULES) return fail(h, -ENOSPC, "sfc_acl_add: table full");
     if (h->rs.next_acl_id >= SFC_MAX_ACL_RULES) return fail(h, -ENOSPC, "sfc_acl_add: rule ids exhausted (sfc_clear)");
     if (rule->ip_ver != 0 && rule->ip_ver != 4 && rule->ip_ver != 6) return fail(h, -EINVAL, "sfc_acl_add: ip_ver");
@@ -579,6 +612,7 @@ int sfc_acl_add(sfc_handle* h, const sfc_acl_rule* rule, uint32_t* rule_id) {
 
 int sfc_acl_del(sfc_handle* h, uint32_t rule_id) {
     if (!h) return -EINVAL;
+    h->rs.other_dirty = true;  // not a flow edit: the next commit rebuilds the image
     for (size_t i = 0; i < h->rs.acl.size(); ++i)
         if (h->rs.acl[i].id == rule_id) {
             h->rs.acl.erase(h->rs.acl.begin() + i);
@@ -594,12 +628,37 @@ int sfc_clear(sfc_handle* h) {
 }
 
 // =================================================================== commit / image ======
-int sfc_commit(sfc_handle* h) {
-    if (!h) return -EINVAL;
-    DeviceGuard g(h->device);
+}  // extern "C" (reopened below)
+
+namespace {
+
+// Point the host shadows at a freshly built image (kept in shadowN_mem) so later flow edits can be
+// applied to single buckets.
+void adopt_shadows(sfc_handle* h, const std::vector<uint8_t>& img) {
+    memcpy(&h->header, img.data(), sizeof(ImageHeader));
+    const ImageHeader& H = h->header;
+    auto take = [&](FlowTable& t, std::vector<uint32_t>& mem, bool v6, uint64_t off, uint32_t nb, uint32_t nhash, uint64_t seed) {
+        t = FlowTable();
+        t.v6 = v6;
+        mem.assign((const uint32_t*)(img.data() + off), (const uint32_t*)(img.data() + off) + (size_t)nb * t.words());
+        t.tab = mem.data();
+        t.nbuckets = nb;
+        t.nhash = (int)nhash;
+        expand_seed(seed, t.S, v6 ? kFlow6SeedWords : kFlow4SeedWords);
+    };
+    take(h->shadow4, h->shadow4_mem, false, H.flow4_off, H.flow4_nbuckets, H.flow4_nhash, H.flow4_seed);
+    take(h->shadow6, h->shadow6_mem, true, H.flow6_off, H.flow6_nbuckets, H.flow6_nhash, H.flow6_seed);
+    h->shadow_valid = true;
+}
+
+int full_commit(sfc_handle* h) {
     std::vector<uint8_t> img;
     std::string err;
     if (!build_image(h->rs, h->epoch + 1, img, err)) return fail(h, -ENOSPC, "sfc_commit: %s", err.c_str());
+    adopt_shadows(h, img);
+    h->rs.flow_log.clear();
+    h->rs.other_dirty = false;
+    ++h->n_full_commits;
     if (h->offline()) {
         h->host_image.swap(img);
         h->image_bytes = h->host_image.size();
@@ -607,6 +666,124 @@ int sfc_commit(sfc_handle* h) {
         return 0;
     }
     return install_image_from_host(h, img.data(), img.size());
+}
+
+// Apply the logged flow edits to the shadows and ship only the buckets they touched.
+// Returns 1 if done, 0 if a full rebuild is needed (nothing has been changed on the device then), < 0 on error.
+int incremental_commit(sfc_handle* h, cudaStream_t st, bool async) {
+    RuleStore& rs = h->rs;
+    if (rs.other_dirty || !h->shadow_valid || (!h->offline() && !h->d_image)) return 0;
+    const int max_load = rs.flow_hashes == 2 ? 45 : 85;
+    long c4 = h->header.flow4_count, c6 = h->header.flow6_count;
+    for (auto& ch : rs.flow_log) (ch.rec.ip_ver == 6 ? c6 : c4) += ch.add ? 1 : -1;
+    if (c4 * 100 > (long)h->shadow4.nbuckets * max_load || c6 * 100 > (long)h->shadow6.nbuckets * max_load) return 0;
+    std::vector<uint32_t> dirty4, dirty6;
+    // A failed insertion walk leaves the shadow with one flow homeless: fall back to a rebuild, which
+    // re-adopts the shadows from the rule store (the source of truth).  Nothing has reached the device yet.
+    uint32_t rec[kFlow6BucketWords];
+    for (auto& ch : rs.flow_log) {
+        const FlowRec& f = ch.rec;
+        FlowTable& t = f.ip_ver == 6 ? h->shadow6 : h->shadow4;
+        std::vector<uint32_t>& dirty = f.ip_ver == 6 ? dirty6 : dirty4;
+        FlowTable::encode(f, f.action == SFC_ACT_FORWARD ? nf_of_port(rs, f.out_port) : (uint32_t)SFC_NF_NONE, rec);
+        bool ok = ch.add ? t.insert(rec, &dirty) : t.erase(rec, &dirty);
+        if (!ok) {
+            h->shadow_valid = false;  // shadow no longer mirrors the device; the rebuild restores it
+            return 0;
+        }
+    }
+    auto uniq = [](std::vector<uint32_t>& v) {
+        std::sort(v.begin(), v.end());
+        v.erase(std::unique(v.begin(), v.end()), v.end());
+    };
+    uniq(dirty4);
+    uniq(dirty6);
+    h->header.flow4_count = (uint32_t)c4;
+    h->header.flow6_count = (uint32_t)c6;
+    h->header.epoch = h->epoch + 1;
+    if (h->offline()) {
+        for (uint32_t b : dirty4)
+            memcpy(h->host_image.data() + h->header.flow4_off + (size_t)b * kFlow4BucketBytes, h->shadow4.tab + (size_t)b * kFlow4BucketWords, kFlow4BucketBytes);
+        for (uint32_t b : dirty6)
+            memcpy(h->host_image.data() + h->header.flow6_off + (size_t)b * kFlow6BucketBytes, h->shadow6.tab + (size_t)b * kFlow6BucketWords, kFlow6BucketBytes);
+        memcpy(h->host_image.data(), &h->header, sizeof(ImageHeader));
+    } else {
+        // staging layout: [idx4][idx6][data4][data6][header]
+        size_t n4 = dirty4.size(), n6 = dirty6.size();
+        size_t need = (n4 + n6) * 4 + n4 * kFlow4BucketBytes + n6 * kFlow6BucketBytes + sizeof(ImageHeader) + 64;
+        if (!h->patch_done) CUDA_TRY(h, cudaEventCreateWithFlags(&h->patch_done, cudaEventDisableTiming));
+        else CUDA_TRY(h, cudaEventSynchronize(h->patch_done));  // the previous patch has left the staging buffer
+        if (need > h->patch_cap) {
+            if (h->h_patch) cudaFreeHost(h->h_patch);
+            if (h->d_patch) cudaFree(h->d_patch);
+            h->patch_cap = std::max<size_t>(need * 2, 1 << 20);
+            CUDA_TRY(h, cudaMallocHost(&h->h_patch, h->patch_cap));
+            CUDA_TRY(h, cudaMalloc(&h->d_patch, h->patch_cap));
+        }
+        uint8_t* p = h->h_patch;
+        size_t o_idx4 = 0, o_idx6 = n4 * 4, o_d4 = (n4 + n6) * 4, o_d6 = o_d4 + n4 * kFlow4BucketBytes,
+               o_hdr = (o_d6 + n6 * kFlow6BucketBytes + 15) & ~(size_t)15;
+        if (n4) memcpy(p + o_idx4, dirty4.data(), n4 * 4);
+        if (n6) memcpy(p + o_idx6, dirty6.data(), n6 * 4);
+        for (size_t i = 0; i < n4; ++i) memcpy(p + o_d4 + i * kFlow4BucketBytes, h->shadow4.tab + (size_t)dirty4[i] * kFlow4BucketWords, kFlow4BucketBytes);
+        for (size_t i = 0; i < n6; ++i) memcpy(p + o_d6 + i * kFlow6BucketBytes, h->shadow6.tab + (size_t)dirty6[i] * kFlow6BucketWords, kFlow6BucketBytes);
+        memcpy(p + o_hdr, &h->header, sizeof(ImageHeader));
+        CUDA_TRY(h, cudaMemcpyAsync(h->d_patch, p, o_hdr + sizeof(ImageHeader), cudaMemcpyHostToDevice, st));
+        if (n4) {
+            unsigned threads = (unsigned)(n4 * kFlow4BucketWords);
+            patch_buckets_kernel<<<(threads + 255) / 256, 256, 0, st>>>((uint32_t*)(h->d_image + h->header.flow4_off), (const uint32_t*)(h->d_patch + o_idx4),
+                                                                       (const uint32_t*)(h->d_patch + o_d4), (uint32_t)n4, kFlow4BucketWords);
+            ++h->launches;
+        }
+        if (n6) {
+            unsigned threads = (unsigned)(n6 * kFlow6BucketWords);
+            patch_buckets_kernel<<<(threads + 255) / 256, 256, 0, st>>>((uint32_t*)(h->d_image + h->header.flow6_off), (const uint32_t*)(h->d_patch + o_idx6),
+                                                                       (const uint32_t*)(h->d_patch + o_d6), (uint32_t)n6, kFlow6BucketWords);
+            ++h->launches;
+        }
+        CUDA_TRY(h, cudaGetLastError());
+        CUDA_TRY(h, cudaMemcpyAsync(h->d_image, h->d_patch + o_hdr, sizeof(ImageHeader), cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(h, cudaEventRecord(h->patch_done, st));
+        if (!async) CUDA_TRY(h, cudaStreamSynchronize(st));
+        h->T.flow4_count = (uint32_t)c4;  // the kernel takes its table descriptor by value at launch
+        h->T.flow6_count = (uint32_t)c6;
+    }
+    ++h->epoch;
+    h->n_patched_buckets += dirty4.size() + dirty6.size();
+    ++h->n_incremental_commits;
+    rs.flow_log.clear();
+    return 1;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sfc_commit(sfc_handle* h) {
+    if (!h) return -EINVAL;
+    DeviceGuard g(h->device);
+    int rc = incremental_commit(h, nullptr, false);
+    if (rc != 0) return rc < 0 ? rc : 0;
+    return full_commit(h);
+}
+
+int sfc_commit_stream(sfc_handle* h, void* cuda_stream) {
+    if (!h) return -EINVAL;
+    DeviceGuard g(h->device);
+    int rc = incremental_commit(h, (cudaStream_t)cuda_stream, true);
+    if (rc != 0) return rc < 0 ? rc : 0;
+    return full_commit(h);
+}
+
+long sfc_stat(const sfc_handle* h, const char* name) {
+    if (!h || !name) return -EINVAL;
+    if (!strcmp(name, "full_commits")) return (long)h->n_full_commits;
+    if (!strcmp(name, "incremental_commits")) return (long)h->n_incremental_commits;
+    if (!strcmp(name, "patched_buckets")) return (long)h->n_patched_buckets;
+    if (!strcmp(name, "flows")) return (long)h->rs.flows.size();
+    if (!strcmp(name, "flow4_first_bucket")) return (long)h->flow_first[0];
+    if (!strcmp(name, "launches")) return (long)h->launches;
+    return -ENOENT;
 }
 
 size_t sfc_table_size(const sfc_handle* h) { return h ? h->image_bytes : 0; }
@@ -631,6 +808,8 @@ int sfc_table_export(const sfc_handle* hc, void* buf, size_t len) {
 int sfc_table_import(sfc_handle* h, const void* buf, size_t len) {
     if (!h || !buf) return -EINVAL;
     if (const char* why = validate_image((const uint8_t*)buf, len)) return fail(h, -EINVAL, "sfc_table_import: %s", why);
+    h->shadow_valid = false;  // an imported image is not described by this handle's rule store
+    h->rs.other_dirty = true;
     if (h->offline()) {
         h->host_image.assign((const uint8_t*)buf, (const uint8_t*)buf + len);
         h->image_bytes = len;
@@ -678,6 +857,8 @@ int sfc_table_import_device(sfc_handle* h, const void* dptr, size_t len, void* c
     if (h->d_image) cudaFree(h->d_image);
     h->d_image = d;
     h->image_bytes = len;
+    h->shadow_valid = false;
+    h->rs.other_dirty = true;
     bind_tables(h);
     return 0;
 }

@@ -57,6 +57,38 @@ void FlowIndex::insert(const std::vector<FlowRec>& recs, uint32_t pos) {
     ++used_;
 }
 
+int64_t FlowIndex::slot_of(const std::vector<FlowRec>& recs, uint32_t pos) const {
+    size_t mask = slots_.size() - 1;
+    for (size_t i = hash(recs[pos]) & mask;; i = (i + 1) & mask) {
+        if (!slots_[i]) return -1;
+        if (slots_[i] == pos + 1) return (int64_t)i;
+    }
+}
+void FlowIndex::erase(std::vector<FlowRec>& recs, uint32_t pos) {
+    size_t mask = slots_.size() - 1;
+    int64_t hole = slot_of(recs, pos);
+    uint32_t last = (uint32_t)recs.size() - 1;
+    int64_t last_slot = last != pos ? slot_of(recs, last) : -1;
+    if (last_slot >= 0) slots_[last_slot] = pos + 1;  // the last record is about to move to `pos`
+    // backward-shift deletion starting at the hole
+    size_t i = (size_t)hole;
+    slots_[i] = 0;
+    for (size_t j = (i + 1) & mask; slots_[j]; j = (j + 1) & mask) {
+        uint32_t p = slots_[j] - 1;
+        const FlowRec& r = (p == pos && last != pos) ? recs[last] : recs[p];  // slot re-pointed above still hashes as `last`
+        size_t home = hash(r) & mask;
+        bool movable = ((j - home) & mask) >= ((j - i) & mask);
+        if (movable) {
+            slots_[i] = slots_[j];
+            slots_[j] = 0;
+            i = j;
+        }
+    }
+    --used_;
+    if (last != pos) recs[pos] = recs[last];
+    recs.pop_back();
+}
+
 void RuleStore::clear_rules() {
     l2.clear();
     next_l2_id = 0;
@@ -65,6 +97,8 @@ void RuleStore::clear_rules() {
     flows.clear();
     flow_index.clear();
     next_flow_id = 0;
+    flow_log.clear();
+    other_dirty = true;
     lpm4.clear();
     lpm6.clear();
     next_lpm_id = 0;
@@ -116,6 +150,103 @@ bool flow_from_key(const sfc_flow_key& k, const sfc_flow_action& a, FlowRec& out
     return true;
 }
 
+// ------------------------------------------------------------------ FlowTable ------------
+uint8_t nf_of_port(const RuleStore& rs, uint32_t port) {
+    for (size_t i = 0; i < rs.nf_in.size(); ++i)
+        if (rs.nf_in[i] == port || rs.nf_out[i] == port) return (uint8_t)i;  // lowest NF index wins
+    return (uint8_t)SFC_NF_NONE;
+}
+
+void FlowTable::encode(const FlowRec& f, uint32_t next_nf, uint32_t* rec) {
+    const bool six = f.ip_ver == 6;
+    const int bw = six ? kFlow6BucketWords : kFlow4BucketWords;
+    for (int w = 0; w < bw; ++w) rec[w] = 0;
+    int t;
+    if (!six) {
+        rec[0] = f.sip[0];
+        rec[1] = f.dip[0];
+        rec[2] = f.ports;
+        t = 3;
+    } else {
+        for (int w = 0; w < 4; ++w) {
+            rec[w] = f.sip[w];
+            rec[4 + w] = f.dip[w];
+        }
+        rec[8] = f.ports;
+        t = 9;
+    }
+    rec[t] = (f.meta & 0xFFFFFu) | kSlotValid;
+    rec[t + 1] = res_hi(f.action, next_nf, f.out_port);
+    rec[t + 2] = res_lo(SFC_STAGE_FLOW, f.id);
+}
+
+void FlowTable::buckets_of(const uint32_t* rec, uint32_t* b) const {
+    uint32_t x, y;
+    if (v6) {
+        flow6_hash(rec, rec + 4, rec[8], rec[9] & 0xFFFFFu, S, x, y);
+        for (int j = 0; j < nhash; ++j) b[j] = flow_bucket(x, y, j, S + 10, nbuckets);
+    } else {
+        flow4_hash(rec[0], rec[1], rec[2], rec[3] & 0xFFFFFu, S, x, y);
+        for (int j = 0; j < nhash; ++j) b[j] = flow_bucket(x, y, j, S + 4, nbuckets);
+    }
+}
+
+bool FlowTable::insert(const uint32_t* rec, std::vector<uint32_t>* dirty) {
+    const int BW = words(), TAG = tag_index();
+    uint32_t cur[kFlow6BucketWords], tmp[kFlow6BucketWords];
+    memcpy(cur, rec, 4 * BW);
+    uint32_t came_from = 0xFFFFFFFFu;
+    for (int kick = 0; kick < 4000; ++kick) {
+        uint32_t b[kMaxHashes];
+        buckets_of(cur, b);
+        for (int j = 0; j < nhash; ++j) {
+            uint32_t* p = tab + (size_t)b[j] * BW;
+            if (!(p[TAG] & kSlotValid)) {
+                memcpy(p, cur, 4 * BW);
+                if (dirty) dirty->push_back(b[j]);
+                return true;
+            }
+        }
+        rng = mix64(rng + kGamma);
+        int j = (int)(rng % (uint64_t)nhash);
+        if (b[j] == came_from) j = (j + 1) % nhash;
+        uint32_t* p = tab + (size_t)b[j] * BW;
+        memcpy(tmp, p, 4 * BW);
+        memcpy(p, cur, 4 * BW);
+        memcpy(cur, tmp, 4 * BW);
+        if (dirty) dirty->push_back(b[j]);
+        came_from = b[j];
+    }
+    return false;  // the caller rebuilds the table (new seed / more buckets)
+}
+
+bool FlowTable::erase(const uint32_t* rec, std::vector<uint32_t>* dirty) {
+    const int BW = words(), TAG = tag_index();
+    uint32_t b[kMaxHashes];
+    buckets_of(rec, b);
+    for (int j = 0; j < nhash; ++j) {
+        uint32_t* p = tab + (size_t)b[j] * BW;
+        if ((p[TAG] & kSlotValid) && p[TAG] == rec[TAG] && !memcmp(p, rec, 4 * TAG)) {  // key words precede the tag
+            memset(p, 0, 4 * BW);
+            if (dirty) dirty->push_back(b[j]);
+            return true;
+        }
+    }
+    return false;
+}
+
+uint32_t FlowTable::count_first() const {
+    const int BW = words(), TAG = tag_index();
+    uint32_t n = 0, b[kMaxHashes];
+    for (uint32_t i = 0; i < nbuckets; ++i) {
+        const uint32_t* p = tab + (size_t)i * BW;
+        if (!(p[TAG] & kSlotValid)) continue;
+        buckets_of(p, b);
+        n += b[0] == i;
+    }
+    return n;
+}
+
 // ------------------------------------------------------------------ image assembly -------
 namespace {
 
@@ -135,81 +266,14 @@ struct Blob {
 };
 
 // ---- cuckoo ------------------------------------------------------------------------------
-// One slot per bucket; V6 selects the 16-word bucket / IPv6 hash.
-template <bool V6>
-struct Cuckoo {
-    static constexpr int BW = V6 ? kFlow6BucketWords : kFlow4BucketWords;
-    static constexpr int TAG = V6 ? 9 : 3;  // word index of the tag
-    uint32_t* tab;
-    uint32_t nbuckets;
-    int nhash;
-    uint32_t S[16];
-    uint64_t rng = 0x1234567ull;
-
-    void buckets(const uint32_t* rec, uint32_t* b) const {
-        uint32_t x, y;
-        if (V6) {
-            flow6_hash(rec, rec + 4, rec[8], rec[9] & 0xFFFFFu, S, x, y);
-            for (int j = 0; j < nhash; ++j) b[j] = flow_bucket(x, y, j, S + 10, nbuckets);
-        } else {
-            flow4_hash(rec[0], rec[1], rec[2], rec[3] & 0xFFFFFu, S, x, y);
-            for (int j = 0; j < nhash; ++j) b[j] = flow_bucket(x, y, j, S + 4, nbuckets);
-        }
-    }
-    bool insert(const uint32_t* rec) {
-        uint32_t cur[BW], tmp[BW];
-        memcpy(cur, rec, sizeof(cur));
-        uint32_t came_from = 0xFFFFFFFFu;
-        for (int kick = 0; kick < 4000; ++kick) {
-            uint32_t b[kMaxHashes];
-            buckets(cur, b);
-            for (int j = 0; j < nhash; ++j) {
-                uint32_t* p = tab + (size_t)b[j] * BW;
-                if (!(p[TAG] & kSlotValid)) {
-                    memcpy(p, cur, 4 * BW);
-                    return true;
-                }
-            }
-            rng = mix64(rng + kGamma);
-            int j = (int)(rng % (uint64_t)nhash);
-            if (b[j] == came_from) j = (j + 1) % nhash;
-            uint32_t* p = tab + (size_t)b[j] * BW;
-            memcpy(tmp, p, 4 * BW);
-            memcpy(p, cur, 4 * BW);
-            memcpy(cur, tmp, 4 * BW);
-            came_from = b[j];
-        }
-        return false;
-    }
-    // how many occupied slots sit in their first-choice bucket (reported, and used by tests)
-    uint32_t count_first() const {
-        uint32_t n = 0, b[kMaxHashes];
-        for (uint32_t i = 0; i < nbuckets; ++i) {
-            const uint32_t* p = tab + (size_t)i * BW;
-            if (!(p[TAG] & kSlotValid)) continue;
-            buckets(p, b);
-            n += b[0] == i;
-        }
-        return n;
-    }
-};
-
-uint8_t nf_of_port(const RuleStore& rs, uint32_t port) {
-    for (size_t i = 0; i < rs.nf_in.size(); ++i)
-        if (rs.nf_in[i] == port || rs.nf_out[i] == port) return (uint8_t)i;  // lowest NF index wins
-    return (uint8_t)SFC_NF_NONE;
-}
-
-template <bool V6>
-bool build_cuckoo(Blob& blob, const RuleStore& rs, const std::vector<const FlowRec*>& recs, uint64_t& off,
+bool build_cuckoo(Blob& blob, const RuleStore& rs, bool v6, const std::vector<const FlowRec*>& recs, uint64_t& off,
                   uint32_t& nbuckets, uint64_t& seed_out, uint32_t& first_out, std::string& err) {
-    constexpr int BW = Cuckoo<V6>::BW;
+    const int BW = v6 ? kFlow6BucketWords : kFlow4BucketWords;
     size_t n = recs.size();
     int nhash = rs.flow_hashes;
     int max_load = nhash == 2 ? 45 : 85;
     int load_pct = std::min(std::max(rs.flow_load_pct, 5), max_load);
     uint64_t nb = std::max<uint64_t>(8, (n * 100 + (uint64_t)load_pct - 1) / (uint64_t)load_pct);
-    // precompute next_nf per port once
     std::vector<uint8_t> nf(SFC_MAX_PORTS, (uint8_t)SFC_NF_NONE);
     for (uint32_t p = 0; p < SFC_MAX_PORTS; ++p) nf[p] = nf_of_port(rs, p);
     for (int grow = 0; grow < 6; ++grow, nb = nb + nb / 8 + 1) {
@@ -217,36 +281,19 @@ bool build_cuckoo(Blob& blob, const RuleStore& rs, const std::vector<const FlowR
         for (int attempt = 0; attempt < 4; ++attempt) {
             size_t start = blob.img.size();
             off = blob.reserve((size_t)nb * BW * 4, 0x00);
-            Cuckoo<V6> c;
+            FlowTable c;
+            c.v6 = v6;
             c.tab = blob.at<uint32_t>(off);
             c.nbuckets = (uint32_t)nb;
             c.nhash = nhash;
-            uint64_t seed = mix64(0x5FC0C0DEull + 977ull * attempt + 31ull * grow + (V6 ? 7ull : 0ull));
-            expand_seed(seed, c.S, V6 ? kFlow6SeedWords : kFlow4SeedWords);
+            uint64_t seed = mix64(0x5FC0C0DEull + 977ull * attempt + 31ull * grow + (v6 ? 7ull : 0ull));
+            expand_seed(seed, c.S, v6 ? kFlow6SeedWords : kFlow4SeedWords);
             bool ok = true;
-            uint32_t rec[BW];
+            uint32_t rec[kFlow6BucketWords];
             for (size_t i = 0; i < n && ok; ++i) {
                 const FlowRec& f = *recs[i];
-                for (int w = 0; w < BW; ++w) rec[w] = 0;
-                int t;
-                if (!V6) {
-                    rec[0] = f.sip[0];
-                    rec[1] = f.dip[0];
-                    rec[2] = f.ports;
-                    t = 3;
-                } else {
-                    for (int w = 0; w < 4; ++w) {
-                        rec[w] = f.sip[w];
-                        rec[4 + w] = f.dip[w];
-                    }
-                    rec[8] = f.ports;
-                    t = 9;
-                }
-                rec[t] = (f.meta & 0xFFFFFu) | kSlotValid;
-                uint32_t nfv = f.action == SFC_ACT_FORWARD ? nf[f.out_port] : (uint32_t)SFC_NF_NONE;
-                rec[t + 1] = res_hi(f.action, nfv, f.out_port);
-                rec[t + 2] = res_lo(SFC_STAGE_FLOW, f.id);
-                ok = c.insert(rec);
+                FlowTable::encode(f, f.action == SFC_ACT_FORWARD ? nf[f.out_port] : (uint32_t)SFC_NF_NONE, rec);
+                ok = c.insert(rec, nullptr);
             }
             if (ok) {
                 nbuckets = (uint32_t)nb;
@@ -615,8 +662,8 @@ bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& imag
     H.flow4_count = (uint32_t)f4.size();
     H.flow6_count = (uint32_t)f6.size();
     H.flow4_nhash = H.flow6_nhash = (uint32_t)rs.flow_hashes;
-    if (!build_cuckoo<false>(blob, rs, f4, H.flow4_off, H.flow4_nbuckets, H.flow4_seed, H.flow4_first, err)) return false;
-    if (!build_cuckoo<true>(blob, rs, f6, H.flow6_off, H.flow6_nbuckets, H.flow6_seed, H.flow6_first, err)) return false;
+    if (!build_cuckoo(blob, rs, false, f4, H.flow4_off, H.flow4_nbuckets, H.flow4_seed, H.flow4_first, err)) return false;
+    if (!build_cuckoo(blob, rs, true, f6, H.flow6_off, H.flow6_nbuckets, H.flow6_seed, H.flow6_first, err)) return false;
 
     // L2 steering: resolve OpenFlow priorities per match, exact and wildcard apart
     {

@@ -53,12 +53,43 @@ class FlowIndex {
     int64_t find(const std::vector<FlowRec>& recs, const FlowRec& k) const;
     void insert(const std::vector<FlowRec>& recs, uint32_t pos);
     void rebuild(const std::vector<FlowRec>& recs, size_t expect);
+    // Remove recs[pos] from BOTH the index and the vector in O(1): the last record moves into the
+    // hole and its index slot is re-pointed (backward-shift deletion keeps probe chains intact).
+    void erase(std::vector<FlowRec>& recs, uint32_t pos);
 
   private:
     std::vector<uint32_t> slots_;  // pos+1, 0 = empty
     size_t used_ = 0;
     static uint64_t hash(const FlowRec& k);
     void grow(const std::vector<FlowRec>& recs, size_t want);
+    int64_t slot_of(const std::vector<FlowRec>& recs, uint32_t pos) const;
+};
+
+// One cuckoo flow table (IPv4: 8-word buckets, IPv6: 16-word buckets) as plain host memory, with
+// the insert / erase walks.  Used twice: by build_image() on the image being assembled, and as the
+// host SHADOW of the committed table so that flow adds and deletes can be applied bucket by bucket
+// (sfc_commit's incremental path) instead of rebuilding and re-uploading the whole image.
+struct FlowTable {
+    bool v6 = false;
+    uint32_t* tab = nullptr;  // nbuckets * words() u32
+    uint32_t nbuckets = 0;
+    int nhash = 2;
+    uint32_t S[16] = {0};
+    uint64_t rng = 0x1234567ull;
+
+    int words() const { return v6 ? kFlow6BucketWords : kFlow4BucketWords; }
+    int tag_index() const { return v6 ? 9 : 3; }
+    void buckets_of(const uint32_t* rec, uint32_t* b) const;
+    // rec = one bucket image (see encode()); every bucket written is appended to *dirty if given
+    bool insert(const uint32_t* rec, std::vector<uint32_t>* dirty);
+    bool erase(const uint32_t* rec, std::vector<uint32_t>* dirty);
+    uint32_t count_first() const;
+    static void encode(const FlowRec& f, uint32_t next_nf, uint32_t* rec);  // fills words() words
+};
+
+struct FlowChange {
+    bool add;
+    FlowRec rec;
 };
 
 struct RuleStore {
@@ -74,6 +105,8 @@ struct RuleStore {
     std::vector<FlowRec> flows;
     FlowIndex flow_index;
     uint32_t next_flow_id = 0;
+    std::vector<FlowChange> flow_log;  // flow edits since the last commit, in order
+    bool other_dirty = true;           // anything but flows changed since the last commit
     // LPM
     typedef std::array<uint32_t, 5> LpmKey;  // len, w[0..3]
     std::map<LpmKey, LpmRec> lpm4, lpm6;
@@ -93,6 +126,7 @@ bool flow_from_key(const sfc_flow_key& k, const sfc_flow_action& a, FlowRec& out
 
 // Build the image.  Returns false and sets err on failure (e.g. cuckoo build could not converge).
 bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& image, std::string& err);
+uint8_t nf_of_port(const RuleStore& rs, uint32_t port);
 
 // Structural validation of an image received from elsewhere (import / broadcast).
 // Returns nullptr if the image is sound, else a static message.  Touches no heap.

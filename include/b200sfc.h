@@ -235,6 +235,22 @@ int sfc_clear(sfc_handle* h);
  * OVS applies each `add-flow` immediately; here edits are batched into epochs. */
 int sfc_commit(sfc_handle* h);
 
+/* Same, ordered on a stream instead of synchronising the device: when only flows were added or
+ * deleted since the last commit (and the table has room), the edits are applied to a host shadow of
+ * the cuckoo table and ONLY the touched buckets are shipped and written in place by a small kernel
+ * on `cuda_stream` — O(edits), no rebuild, no device-wide sync; classify launches queued behind it on
+ * the same stream see the new flows, launches before it the old ones.  Anything else (L2 rules,
+ * prefixes, ACL, chain, options, a table that must grow) falls back to the full rebuild of sfc_commit.
+ * sfc_commit itself takes the same incremental path when it can, then waits for it.
+ * Reference anchor: per-pod rule churn — CreateBridgePort / DeleteBridgePort adding and removing
+ * three flows each (marvell/main.go:383-403, 441-460) — which OVS applies one `add-flow` at a time. */
+int sfc_commit_stream(sfc_handle* h, void* cuda_stream);
+
+/* Counters of the library itself (not of traffic): "full_commits", "incremental_commits",
+ * "patched_buckets", "flows", "flow4_first_bucket", "launches".  Negative errno for unknown names.
+ * Reference anchor: the health/stat surface of DeviceService.GetDevices (marvell/main.go:219-236). */
+long sfc_stat(const sfc_handle* h, const char* name);
+
 /* Size in bytes of the current committed image, and its epoch (number of commits so far). */
 size_t sfc_table_size(const sfc_handle* h);
 uint64_t sfc_table_epoch(const sfc_handle* h);

@@ -130,6 +130,38 @@ def cfg5():
            dict(table_bytes=dp.table_size, build_seconds=build_s))
 
 
+def churn():
+    """Row f3: cost of flow churn on a 1 Mi-flow table — edits per second through the incremental commit,
+    and what a classify launch queued right behind a commit pays."""
+    dp = sfc.Dataplane(0)
+    spec = config3_spec(n_flows=(1 << 20) + 400000, n_ports=17, v6_permille=0)
+    keys, acts = sfc.gen_flows(spec, 0, (1 << 20) + 400000)
+    dp.flow_add_bulk(keys[: 1 << 20], acts[: 1 << 20])
+    t = time.perf_counter(); dp.commit(); full_s = time.perf_counter() - t
+    M = 1 << 20
+    hdr, ports = gen(dp, spec, M)
+    res = torch.zeros(M, dtype=torch.int64, device="cuda")
+    nxt, dead = 1 << 20, 0
+    for edits in (64, 1024, 16384):
+        times = []
+        for rep in range(6):
+            t0 = time.perf_counter()
+            dp.flow_add_bulk(keys[nxt:nxt + edits // 2], acts[nxt:nxt + edits // 2]); nxt += edits // 2
+            for k in keys[dead:dead + edits // 2]:
+                dp.flow_del(k)
+            dead += edits // 2
+            t1 = time.perf_counter()
+            dp.commit_stream(st)
+            dp.classify(hdr.data_ptr(), ports.data_ptr(), res.data_ptr(), M, 0, st)
+            torch.cuda.synchronize()
+            t2 = time.perf_counter()
+            times.append((t1 - t0, t2 - t1))
+        stage, commit = min(x[0] for x in times), min(x[1] for x in times)
+        print(json.dumps(dict(config="churn", flows=1 << 20, edits_per_commit=edits, stage_seconds=stage, commit_plus_1Mi_classify_seconds=commit,
+                              edits_per_second=edits / (stage + commit), full_rebuild_seconds=full_s,
+                              incremental_commits=dp.stat("incremental_commits"), full_commits=dp.stat("full_commits"))), flush=True)
+
+
 for name in sys.argv[1:] or ["cfg3", "cfg4", "cfg5"]:
     globals()[name]()
     torch.cuda.empty_cache()
