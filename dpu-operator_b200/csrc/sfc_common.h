@@ -39,8 +39,6 @@ struct Key {
     uint32_t ports;
     uint32_t meta;
     uint32_t ip_ver;  // 0 (non-IP), 4, 6
-    uint32_t mac_hi;  // dst MAC bytes 0..1
-    uint32_t mac_lo;  // dst MAC bytes 2..5
 };
 
 // ---------------------------------------------------------------- result words -----------
