@@ -10,8 +10,8 @@ pytestmark = pytest.mark.gpu
 
 
 def classify_dev(torch, dp, hdr_np, ports_np, flags=0):
-    hdr = torch.from_numpy(np.ascontiguousarray(hdr_np)).cuda()
-    ports = torch.from_numpy(ports_np.view(np.int16)).cuda()
+    hdr = torch.from_numpy(np.array(hdr_np, dtype=np.uint8, order="C")).cuda()  # a copy: frombuffer views are read-only
+    ports = torch.from_numpy(np.array(ports_np, dtype=np.uint16).view(np.int16)).cuda()
     res = torch.zeros(ports_np.size, dtype=torch.int64, device="cuda")
     dp.classify(hdr.data_ptr(), ports.data_ptr(), res.data_ptr(), ports_np.size, flags, torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
@@ -363,3 +363,35 @@ def test_grpc_vsp_drives_the_gpu_dataplane(torch_cuda, tmp_path):
         c.close()
     finally:
         server.stop(0)
+
+
+def test_three_hash_dense_table(torch_cuda):
+    """flow_hashes = 3 at 80 % load: the third bucket choice and the denser table must stay exact."""
+    dp = sfc.Dataplane(0)
+    dp.set_option("flow_hashes", 3)
+    dp.set_option("flow_load_pct", 80)
+    sc = Scenario(dp)
+    spec = config3_spec(n_flows=100000, n_ports=8, v6_permille=300)
+    install_flows(sc, spec)
+    dp.commit()
+    hdr, ports = sfc.gen_packets_host(spec, 0, 150000)
+    assert_same(classify_dev(torch_cuda, dp, hdr, ports), sc.orc.classify(hdr, ports, threads=8), hdr)
+
+
+@pytest.mark.parametrize("feat", [None, "1", "7"])
+def test_acl_3000_rules_single_tree_and_forests(torch_cuda, feat, monkeypatch):
+    """A larger ACL, once with the builder's own choice and once with the rule set forced into
+    category forests (SFC_ACL_FEAT): every shape of the decision structure must give the oracle's verdict."""
+    if feat is not None:
+        monkeypatch.setenv("SFC_ACL_FEAT", feat)
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    spec = config4_spec(n_pfx4=2000, n_pfx6=500, n_acl=3000)
+    install_lpm_acl(sc, spec)
+    dp.commit()
+    hdr, ports = sfc.gen_packets_host(spec, 0, 60000)
+    got = classify_dev(torch_cuda, dp, hdr, ports, consts.F_COUNTERS)
+    want, cnt = sc.orc.classify(hdr, ports, counters=True)
+    assert_same(got, want, hdr)
+    assert np.array_equal(dp.counters_read(), cnt)
+    assert (sfc.result_fields(got)[3] == consts.STAGE_ACL).sum() > 100

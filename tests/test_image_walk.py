@@ -188,3 +188,23 @@ def test_every_ipv4_flow_sits_in_one_of_its_buckets():
         first += j == 0
     assert first / len(range(0, 20000, 7)) > 0.6  # most flows answer on the first probe
     assert abs(img.f4_first / 20000 - first / len(range(0, 20000, 7))) < 0.05  # header statistic is honest
+
+
+def test_forced_forests_answer_like_the_single_tree(monkeypatch):
+    """The category split (SFC_ACL_FEAT) changes the shape of the ACL structure, never its answers."""
+    spec = config4_spec(n_pfx4=500, n_pfx6=100, n_acl=600)
+    hdr, ports = sfc.gen_packets_host(spec, 0, 1500)
+    answers = []
+    for feat in ("0", "1", "5", "7"):
+        monkeypatch.setenv("SFC_ACL_FEAT", feat)
+        sc = Scenario(sfc.Dataplane(-1))
+        install_lpm_acl(sc, spec)
+        sc.dp.commit()
+        img = Image(sc.dp.table_export())
+        out = []
+        for i in range(len(ports)):
+            p, q = acl_key(hdr[i], int(ports[i]))
+            out.append(None if p["ver"] == 0 else img.acl(q))
+        answers.append((img.acl_ntrees, out))
+    assert answers[0][0] == 1 and answers[3][0] > answers[1][0] >= 2
+    assert all(a[1] == answers[0][1] for a in answers[1:])
