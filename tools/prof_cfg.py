@@ -12,6 +12,10 @@ if which == "cfg3":
     topo = sc.build_chain(8, 4)
     spec = config3_spec(n_flows=1 << 20, n_ports=topo["n_ports"])
     install_flows(sc, spec)
+elif which == "cfg3u":  # 1 Mi IPv4 flows, IPv4-only traffic
+    spec = sfc.make_gen_spec(n_flows=1 << 20, hit_permille=950)
+    for f in range(0, 1 << 20, 1 << 18):
+        k, a = sfc.gen_flows(spec, f, 1 << 18); dp.flow_add_bulk(k, a)
 elif which == "cfg4":
     spec = config4_spec(); install_lpm_acl(sc, spec)
 else:
@@ -27,7 +31,9 @@ res = torch.zeros((launches, M), dtype=torch.int64, device="cuda")
 for i in range(launches):
     dp.gen_packets(spec, i * M, M, hdr[i].data_ptr(), ports[i].data_ptr(), st)
 torch.cuda.synchronize()
-for i in range(launches):
-    dp.classify(hdr[i].data_ptr(), ports[i].data_ptr(), res[i].data_ptr(), M, 0, st)
+flags = int(os.environ.get("SFC_FLAGS", "0"))
+for rep in range(int(os.environ.get("SFC_REPS", "1"))):
+    for i in range(launches):
+        dp.classify(hdr[i].data_ptr(), ports[i].data_ptr(), res[i].data_ptr(), M, flags, st)
 torch.cuda.synchronize()
 print("done", which, dp.table_size)
