@@ -113,10 +113,12 @@ void fill_tables(DevTables& T, const ImageHeader& H, const uint8_t* b, unsigned 
     T.flow4_nhash = H.flow4_nhash;
     T.flow4_count = H.flow4_count;
     {   // probe strategy by where the table will live.  Measured on B200 (tools/tune.py): a table of
-        // <= 128 KB stays in L1 and both probes at once win (14.8 vs 15.8 us per 1M packets); for
-        // anything larger the second load only adds L2/DRAM sectors (eager is 8-40% slower).
+        // <= 128 KB stays in L1 and both probes at once win (14.8 vs 15.8 us per 1M packets); one that
+        // stays in L2 next to the packet stream (measured up to 42 MB: 14.3 vs 15.5 us) still gains from
+        // issuing both probes at once, without L1; beyond that every probe is a DRAM sector and the
+        // second load only adds traffic (eager is 8-40% slower).
         uint64_t bytes = (uint64_t)H.flow4_nbuckets * kFlow4BucketBytes;
-        uint32_t mode = bytes <= (128u << 10) ? (kProbeEager | kProbeL1) : 0u;
+        uint32_t mode = bytes <= (128u << 10) ? (kProbeEager | kProbeL1) : bytes <= (48u << 20) ? kProbeEager : 0u;
         if (probe_mode >= 0) mode = (uint32_t)probe_mode;
         T.flow4_mode = mode;
     }

@@ -16,6 +16,11 @@ elif which == "cfg3u":  # 1 Mi IPv4 flows, IPv4-only traffic
     spec = sfc.make_gen_spec(n_flows=1 << 20, hit_permille=950)
     for f in range(0, 1 << 20, 1 << 18):
         k, a = sfc.gen_flows(spec, f, 1 << 18); dp.flow_add_bulk(k, a)
+elif which.startswith("f2^"):  # 2^N IPv4 flows, uniform IPv4-only traffic
+    nf = 1 << int(which[3:])
+    spec = sfc.make_gen_spec(n_flows=nf, hit_permille=950)
+    for f in range(0, nf, 1 << 18):
+        k, a = sfc.gen_flows(spec, f, min(nf, 1 << 18)); dp.flow_add_bulk(k, a)
 elif which == "cfg4":
     spec = config4_spec(); install_lpm_acl(sc, spec)
 else:
@@ -23,6 +28,7 @@ else:
     for first in range(0, 1 << 24, 1 << 20):
         k, a = sfc.gen_flows(spec, first, 1 << 20); dp.flow_add_bulk(k, a)
 dp.commit()
+dp.set_option("flow_probe_mode", int(os.environ.get("SFC_PROBE", "-1")))
 M = 1 << 20
 st = torch.cuda.current_stream().cuda_stream
 hdr = torch.empty((launches, M, 64), dtype=torch.uint8, device="cuda")

@@ -28,6 +28,11 @@ def setup(mode):
         spec = sfc.make_gen_spec(n_flows=1 << 20, hit_permille=950)
         for f in range(0, 1 << 20, 1 << 18):
             k, a = sfc.gen_flows(spec, f, 1 << 18); dp.flow_add_bulk(k, a)
+    elif mode.startswith("f2^"):  # 2^N IPv4 flows, uniform or Zipf ("f2^18z") traffic: the L2 capacity curve
+        lg = int(mode[3:].rstrip("z")); nf = 1 << lg
+        spec = sfc.make_gen_spec(n_flows=nf, hit_permille=950, zipf=int(mode.endswith("z")))
+        for f in range(0, nf, 1 << 18):
+            k, a = sfc.gen_flows(spec, f, min(nf, 1 << 18)); dp.flow_add_bulk(k, a)
     elif mode == "big16m":
         spec = sfc.make_gen_spec(n_flows=1 << 24, hit_permille=950)
         for f in range(0, 1 << 24, 1 << 20):
