@@ -12,6 +12,7 @@ from __future__ import annotations
 
 from .capi import (  # noqa: F401
     ACL_RULE_DTYPE,
+    BATCH_DTYPE,
     FLOW_ACTION_DTYPE,
     FLOW_KEY_DTYPE,
     GEN_SPEC_DTYPE,
@@ -41,6 +42,7 @@ __all__ = [
     "FLOW_KEY_DTYPE",
     "FLOW_ACTION_DTYPE",
     "ACL_RULE_DTYPE",
+    "BATCH_DTYPE",
     "GEN_SPEC_DTYPE",
     "make_gen_spec",
     "gen_flows",

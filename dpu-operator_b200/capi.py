@@ -27,6 +27,7 @@ ACL_RULE_DTYPE = np.dtype(
      ("sport", "<u2"), ("sport_mask", "<u2"), ("dport", "<u2"), ("dport_mask", "<u2"),
      ("proto", "u1"), ("proto_mask", "u1"), ("ip_ver", "u1"), ("verdict", "u1"), ("priority", "<u4")]
 )
+BATCH_DTYPE = np.dtype([("hdr", "<u8"), ("in_port", "<u8"), ("result", "<u8"), ("n", "<u4"), ("reserved", "<u4")])
 GEN_SPEC_DTYPE = np.dtype(
     [("seed_pkts", "<u8"), ("seed_rules", "<u8"), ("seed_lpm", "<u8"), ("seed_acl", "<u8"),
      ("n_flows", "<u4"), ("n_ports", "<u4"), ("port_base", "<u4"), ("n_out_ports", "<u4"),
@@ -85,6 +86,7 @@ def _load():
         "sfc_table_export_device": (C.c_int, [vp, vp, C.c_size_t, vp]),
         "sfc_table_import_device": (C.c_int, [vp, vp, C.c_size_t, vp]),
         "sfc_classify": (C.c_int, [vp, vp, vp, vp, C.c_size_t, C.c_uint32, vp]),
+        "sfc_classify_batches": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32, vp]),
         "sfc_classify_host": (C.c_int, [vp, vp, vp, vp, C.c_size_t, C.c_uint32]),
         "sfc_sync": (C.c_int, [vp, vp]),
         "sfc_counters_read": (C.c_int, [vp, u64p, C.c_size_t]),
@@ -292,6 +294,16 @@ class Dataplane:
     # ---- data plane ----
     def classify(self, hdr_ptr: int, in_port_ptr: int, result_ptr: int, n: int, flags: int = 0, stream: int = 0):
         self._chk(lib.sfc_classify(self._h, hdr_ptr, in_port_ptr, result_ptr, n, flags, stream))
+
+    def classify_batches(self, batches, flags: int = 0, stream: int = 0):
+        """``sfc_classify_batches``: ``batches`` is a sequence of (hdr_ptr, in_port_ptr, result_ptr, n)
+        device addresses, or a ready BATCH_DTYPE array."""
+        if not (isinstance(batches, np.ndarray) and batches.dtype == BATCH_DTYPE):
+            arr = np.zeros(len(batches), dtype=BATCH_DTYPE)
+            for i, (hp, pp, rp, n) in enumerate(batches):
+                arr[i] = (hp, pp, rp, n, 0)
+            batches = arr
+        self._chk(lib.sfc_classify_batches(self._h, _ptr(batches), batches.size, flags, stream))
 
     def classify_host(self, hdr: np.ndarray, in_port: np.ndarray, flags: int = 0, out: np.ndarray | None = None):
         hdr = np.ascontiguousarray(hdr, dtype=np.uint8)

@@ -45,11 +45,13 @@ struct sfc_handle {
     unsigned long long* d_counters = nullptr;
     uint64_t launches = 0;
     EncodeTiledFn encode = nullptr;
-    int ctas_per_sm[16] = {0};
+    int ctas_per_sm[20] = {0};  // 0-3 shipped variants, 4-12 tune variants, 16-19 multi-batch variants
     int tune_tile = 0, tune_stages = 0;  // SFC_TUNE=tile,stages (experiments)
     int tune_ctas = 0, tune_carveout = -1;  // cap on resident CTAs per SM / shared-memory carveout percent
     uint32_t flow_first[2] = {0, 0};
     int probe_mode = -1;  // option "flow_probe_mode": -1 auto, else kProbe* bits
+    BatchList batch_list{};               // sfc_classify_batches: the list being laid out for the next launch
+    uintptr_t batch_hdr[kMaxBatches]{};   //   and the header address of each of its entries
     uint32_t* d_tickets = nullptr;  // ring of kTicketRing tile-ticket counters (scratch of the classify kernel)
     // sfc_classify_host staging
     cudaStream_t hs[2] = {nullptr, nullptr};
@@ -219,7 +221,50 @@ int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_
     cfg.attrs = attr;
     cfg.numAttrs = overlap ? 1 : 0;
     CUDA_TRY(h, cudaLaunchKernelEx(&cfg, kern, map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, overlap,
-                                   h->T));
+                                   h->T, NoBatches{}));
+    ++h->launches;
+    return 0;
+}
+
+// One launch over the batches of `L` (already laid out: row0 / tile0 filled in, `rows` = extent of the
+// tensor map in 64-byte records from L.base).
+template <bool C, bool A>
+int launch_multi(sfc_handle* h, int slot, const BatchList& L, uint64_t rows, uint32_t n_tiles, uint32_t flags,
+                 cudaStream_t st) {
+    auto kern = classify_kernel<kTile, kStages, C, A, true>;
+    constexpr int smem = SmemLayout<kTile, kStages, A>::kBytes;
+    if (!h->ctas_per_sm[slot]) {
+        CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        int per = 0;
+        CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, kern, kTile + 32, smem));
+        if (per < 1) return fail(h, -EIO, "classify kernel does not fit on an SM");
+        h->ctas_per_sm[slot] = per;
+    }
+    CUtensorMap map;
+    cuuint64_t dims[2] = {16, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {64};
+    cuuint32_t box[2] = {16, (cuuint32_t)(kTile < 256 ? kTile : 256)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = h->encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<uint8_t*>(L.base), dims, strides, box,
+                           estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(h, -EIO, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    int per_sm = (flags & SFC_F_OVERLAP) ? 1 : h->ctas_per_sm[slot];
+    uint64_t grid = std::min<uint64_t>(n_tiles, (uint64_t)h->sm_count * per_sm);
+    uint32_t* ticket = h->d_tickets + (h->launches % kTicketRing) * kTicketStride;
+    uint32_t overlap = (flags & SFC_F_OVERLAP) ? 1u : 0u;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kTile + 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = overlap ? 1 : 0;
+    CUDA_TRY(h, cudaLaunchKernelEx(&cfg, kern, map, (const uint16_t*)nullptr, (uint64_t*)nullptr, 0u, n_tiles, ticket,
+                                   overlap, h->T, L));
     ++h->launches;
     return 0;
 }
@@ -876,6 +921,65 @@ int sfc_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64
     return launch_classify(h, hdr, in_port, result, n, flags, (cudaStream_t)cuda_stream);
 }
 
+int sfc_classify_batches(sfc_handle* h, const sfc_batch* batches, uint32_t n_batches, uint32_t flags,
+                         void* cuda_stream) {
+    if (!h) return -EINVAL;
+    if (h->offline()) return fail(h, -ENODEV, "offline handle: no device (there is no CPU data path)");
+    if (n_batches == 0) return 0;
+    if (!batches) return fail(h, -EINVAL, "sfc_classify_batches: null batch list");
+    if (!h->d_image) return fail(h, -EINVAL, "sfc_classify_batches: no committed table image (call sfc_commit)");
+    // validate everything before the first launch: a bad descriptor must not leave half the list done
+    for (uint32_t i = 0; i < n_batches; ++i) {
+        const sfc_batch& b = batches[i];
+        if (b.n == 0) continue;
+        if (!b.hdr || !b.in_port || !b.result) return fail(h, -EINVAL, "sfc_classify_batches: null buffer in batch %u", i);
+        if ((uintptr_t)b.hdr & 63) return fail(h, -EINVAL, "sfc_classify_batches: hdr of batch %u is not 64-byte aligned", i);
+        if (b.n > (1u << 30)) return fail(h, -EINVAL, "sfc_classify_batches: batch %u has more than 2^30 packets", i);
+    }
+    DeviceGuard g(h->device);
+    const bool c = flags & SFC_F_COUNTERS, a = h->T.acl_nrules > 0;
+    // Greedy split into launches: at most kMaxBatches descriptors, 2^31 tiles and 2^31 rows of span each
+    // (TMA coordinates are signed 32-bit).
+    constexpr uint64_t kMaxRows = (1ull << 31) - 2 * kTile;
+    BatchList& L = h->batch_list;
+    uint32_t i = 0;
+    while (i < n_batches) {
+        L.count = 0;
+        uintptr_t lo = 0, hi = 0;
+        uint64_t tiles = 0;
+        for (; i < n_batches && L.count < (uint32_t)kMaxBatches; ++i) {
+            const sfc_batch& b = batches[i];
+            if (b.n == 0) continue;
+            const uintptr_t p = (uintptr_t)b.hdr, e = p + (uintptr_t)b.n * 64;
+            const uintptr_t nlo = L.count ? std::min(lo, p) : p, nhi = L.count ? std::max(hi, e) : e;
+            const uint64_t t = (b.n + kTile - 1) / kTile;
+            if (L.count && ((nhi - nlo) / 64 > kMaxRows || tiles + t > (1ull << 31))) break;
+            lo = nlo;
+            hi = nhi;
+            BatchDesc& d = L.b[L.count++];
+            d.row0 = 0;  // filled in below, once the lowest address is known
+            d.n = b.n;
+            d.tile0 = (uint32_t)tiles;
+            d.pad = 0;
+            d.in_port = b.in_port;
+            d.result = b.result;
+            h->batch_hdr[L.count - 1] = p;
+            tiles += t;
+        }
+        if (!L.count) break;  // only empty batches were left
+        L.base = (const uint8_t*)lo;
+        for (uint32_t k = 0; k < L.count; ++k) L.b[k].row0 = (uint32_t)((h->batch_hdr[k] - lo) / 64);
+        const uint64_t rows = (hi - lo) / 64;
+        int rc;
+        if (c && a) rc = launch_multi<true, true>(h, 19, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
+        else if (c) rc = launch_multi<true, false>(h, 18, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
+        else if (a) rc = launch_multi<false, true>(h, 17, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
+        else rc = launch_multi<false, false>(h, 16, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
 int sfc_classify_host(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
                       uint32_t flags) {
     if (!h) return -EINVAL;
@@ -1078,10 +1182,10 @@ extern "C" int sfc_classify_static(int device, const void* image_host, size_t im
     uint32_t* ticket = (uint32_t*)d.area;  // {draw counter, finished producers}: cleared above, reset by the kernel too
     if (acl)
         classify_kernel<kTile, kStages, false, true><<<grid, kTile + 32, SmemLayout<kTile, kStages, true>::kBytes, st>>>(
-            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, 0u, T);
+            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, 0u, T, NoBatches{});
     else
         classify_kernel<kTile, kStages, false, false><<<grid, kTile + 32, SmemLayout<kTile, kStages, false>::kBytes, st>>>(
-            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, 0u, T);
+            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, 0u, T, NoBatches{});
     e = cudaGetLastError();
     if (e != cudaSuccess) return static_fail(errbuf, errlen, -EIO, "kernel launch: %s", cudaGetErrorString(e));
     return 0;

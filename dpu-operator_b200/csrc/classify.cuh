@@ -47,6 +47,40 @@ struct DevTables {
     unsigned long long* counters;
 };
 
+// One launch over several independent packet batches (sfc_classify_batches).  The list travels as a
+// kernel parameter: nothing to allocate or copy, and a captured launch carries its own copy.
+constexpr int kMaxBatches = 512;
+struct BatchDesc {
+    uint32_t row0;   // first record of the batch, in 64-byte rows from BatchList::base
+    uint32_t n;      // packets in the batch
+    uint32_t tile0;  // index of the batch's first tile within the launch
+    uint32_t pad;
+    const uint16_t* in_port;
+    uint64_t* result;
+};
+struct BatchList {
+    const uint8_t* base;  // lowest header address of the launch; the tensor map starts here
+    uint32_t count, pad;
+    BatchDesc b[kMaxBatches];
+};
+struct NoBatches {
+    uint32_t unused;
+};
+template <bool MULTI>
+struct BatchArg {
+    using type = NoBatches;
+};
+template <>
+struct BatchArg<true> {
+    using type = BatchList;
+};
+// what the producer tells the consumers about the tile sitting in a stage (MULTI only)
+struct StageInfo {
+    uint32_t first, rows, raw, pad;
+    const uint16_t* in_port;
+    uint64_t* result;
+};
+
 // ------------------------------------------------------------------ PTX helpers ----------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -92,6 +126,15 @@ __device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map,
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
         " [%0], [%1, {%2, %3}], [%4], %5;" ::"r"(smem_u32(dst)),
         "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)), "l"(policy)
+        : "memory");
+}
+// plain byte copy global -> shared through the same engine (no tensor map, no swizzle): partial tiles
+__device__ __forceinline__ void bulk_load_rows(void* dst, const void* src, uint32_t bytes, uint64_t* bar,
+                                               uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
+            "r"(smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
         : "memory");
 }
 __device__ __forceinline__ uint64_t policy_evict_first() {
@@ -275,10 +318,11 @@ template <int TILE, int STAGES, bool ACL>
 struct SmemLayout {
     static constexpr int kTileBytes = TILE * 64;
     static constexpr int kAclBytes = ACL ? (TILE / 32) * kAclKeyWords * 32 * 4 : 0;
-    static constexpr int kBytes = STAGES * kTileBytes + kAclBytes + 2 * STAGES * 8 + 16 * 8 + 32 * 4 + STAGES * 4 + 16 + 1024;
+    static constexpr int kBytes = STAGES * kTileBytes + kAclBytes + 2 * STAGES * 8 + 16 * 8 + 32 * 4 + STAGES * 4 + 16 +
+                                  STAGES * (int)sizeof(StageInfo) + 1024;
 };
 
-template <int TILE, int STAGES, bool COUNTERS, bool ACL>
+template <int TILE, int STAGES, bool COUNTERS, bool ACL, bool MULTI = false>
 #ifndef SFC_MINB
 #define SFC_MINB 1
 #endif
@@ -287,7 +331,8 @@ __global__ void __launch_bounds__(TILE + 32, SFC_MINB) classify_kernel(const __g
                                                               uint64_t* __restrict__ result, uint32_t n,
                                                               uint32_t n_tiles, uint32_t* ticket,
                                                               uint32_t overlap,
-                                                              const __grid_constant__ DevTables T) {
+                                                              const __grid_constant__ DevTables T,
+                                                              const __grid_constant__ typename BatchArg<MULTI>::type L) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* tiles = smem;
@@ -297,6 +342,7 @@ __global__ void __launch_bounds__(TILE + 32, SFC_MINB) classify_kernel(const __g
     unsigned long long* scnt = (unsigned long long*)(empty + STAGES);  // 16 block-level counters
     uint32_t* dep_sink = (uint32_t*)(scnt + 16);                       // one word per consumer warp
     uint32_t* tile_of = dep_sink + 32;                                 // tile index held by each stage
+    StageInfo* info = (StageInfo*)(((uintptr_t)(tile_of + STAGES) + 15) & ~(uintptr_t)15);
 
     const int tid = threadIdx.x;
     constexpr int kConsumerWarps = TILE / 32;
@@ -334,10 +380,38 @@ __global__ void __launch_bounds__(TILE + 32, SFC_MINB) classify_kernel(const __g
                     mbar_arrive(full + s);  // end marker: no bytes will follow
                     break;
                 }
-                mbar_arrive_expect_tx(full + s, TILE * 64);
+                if constexpr (MULTI) {
+                    // which batch owns this tile: the last one whose first tile is not beyond it
+                    uint32_t lo = 0, hi = L.count;
+                    while (hi - lo > 1) {
+                        const uint32_t mid = (lo + hi) >> 1;
+                        if (L.b[mid].tile0 <= tile) lo = mid; else hi = mid;
+                    }
+                    const uint32_t first = (tile - L.b[lo].tile0) * TILE, left = L.b[lo].n - first;
+                    const uint32_t rows = left < (uint32_t)TILE ? left : (uint32_t)TILE;
+                    const uint32_t row = L.b[lo].row0 + first;
+                    StageInfo& si = info[s];
+                    si.first = first;
+                    si.rows = rows;
+                    si.raw = rows < (uint32_t)TILE;
+                    si.in_port = L.b[lo].in_port;
+                    si.result = L.b[lo].result;
+                    mbar_arrive_expect_tx(full + s, rows * 64);
+                    if (rows == (uint32_t)TILE) {
 #pragma unroll
-                for (int r = 0; r < TILE; r += kBoxRows)  // a TMA box is at most 256 rows
-                    tma_load_tile(tiles + s * TILE * 64 + r * 64, &hdr_map, 0, (int)(tile * TILE) + r, full + s, pol);
+                        for (int r = 0; r < TILE; r += kBoxRows)
+                            tma_load_tile(tiles + s * TILE * 64 + r * 64, &hdr_map, 0, (int)row + r, full + s, pol);
+                    } else {
+                        // the end of a batch: a box would run past it into memory that is not ours, so
+                        // copy exactly the rows that exist, unswizzled (consumers are told: raw)
+                        bulk_load_rows(tiles + s * TILE * 64, L.base + (size_t)row * 64, rows * 64, full + s, pol);
+                    }
+                } else {
+                    mbar_arrive_expect_tx(full + s, TILE * 64);
+#pragma unroll
+                    for (int r = 0; r < TILE; r += kBoxRows)  // a TMA box is at most 256 rows
+                        tma_load_tile(tiles + s * TILE * 64 + r * 64, &hdr_map, 0, (int)(tile * TILE) + r, full + s, pol);
+                }
                 tile = next;
             }
             __threadfence();
@@ -359,14 +433,28 @@ __global__ void __launch_bounds__(TILE + 32, SFC_MINB) classify_kernel(const __g
         mbar_wait(full + s, use & 1);
         const uint32_t tile = tile_of[s];
         if (tile == 0xFFFFFFFFu) break;
-        const uint32_t pkt = tile * TILE + tid;
-        const bool live = pkt < n;
-        const uint32_t port = live ? (uint32_t)__ldg(in_port + pkt) : 0u;
+        uint32_t pkt, swz = sw, info_dep = 0;
+        bool live;
+        const uint16_t* ports_in = in_port;
+        uint64_t* res_out = result;
+        if constexpr (MULTI) {
+            const StageInfo& si = info[s];
+            pkt = si.first + tid;
+            live = (uint32_t)tid < si.rows;
+            if (si.raw) swz = 0;
+            ports_in = si.in_port;
+            res_out = si.result;
+            info_dep = si.first ^ si.rows ^ si.raw ^ (uint32_t)(uintptr_t)ports_in ^ (uint32_t)(uintptr_t)res_out;
+        } else {
+            pkt = tile * TILE + tid;
+            live = pkt < n;
+        }
+        const uint32_t port = live ? (uint32_t)__ldg(ports_in + pkt) : 0u;
         uint32_t w[16];
         const uint32_t base = smem_u32(tiles + s * TILE * 64) + row_off;
 #pragma unroll
         for (uint32_t c = 0; c < 4; ++c) {
-            uint4 v = lds128(base + ((c ^ sw) << 4));
+            uint4 v = lds128(base + ((c ^ swz) << 4));
             w[4 * c + 0] = v.x;
             w[4 * c + 1] = v.y;
             w[4 * c + 2] = v.z;
@@ -378,7 +466,7 @@ __global__ void __launch_bounds__(TILE + 32, SFC_MINB) classify_kernel(const __g
         // B200 as sporadic wrong rows).  Folding one word of each of the four loads into a value
         // that lane 0 stores makes the store — issued in order before the arrive — wait on the
         // warp-wide scoreboard of all four LDS instructions.
-        const uint32_t dep = w[3] ^ w[7] ^ w[11] ^ w[15] ^ tile;
+        const uint32_t dep = w[3] ^ w[7] ^ w[11] ^ w[15] ^ tile ^ info_dep;
         __syncwarp();
         if (lane == 0) {
             asm volatile("st.shared.u32 [%0], %1;" ::"r"(smem_u32(dep_sink + (tid >> 5))), "r"(dep) : "memory");
@@ -523,7 +611,7 @@ __global__ void __launch_bounds__(TILE + 32, SFC_MINB) classify_kernel(const __g
             }
         }
 
-        if (live) stg_result(result + pkt, rlo, rhi);
+        if (live) stg_result(res_out + pkt, rlo, rhi);
 
         if (COUNTERS) {
             uint32_t act = rhi >> 24, stage = rlo >> 28;

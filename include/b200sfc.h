@@ -282,6 +282,24 @@ int sfc_table_import_device(sfc_handle* h, const void* dptr, size_t len, void* c
 int sfc_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result,
                  size_t n, uint32_t flags, void* cuda_stream);
 
+/* Many independent batches in ONE launch (BASELINE.json configs[2]: 4096-packet batches).  A NIC
+ * poll loop hands over bursts far smaller than what keeps 148 SMs busy, and one launch per burst
+ * is bound by launch latency; this call takes the bursts as they are — separate buffers, ragged
+ * sizes — and classifies them as if they were one batch.  `batches` is a HOST array (read before
+ * the call returns, nothing is retained); the buffers it names are DEVICE pointers, each hdr
+ * 64-byte aligned.  Results are exactly those of one sfc_classify per batch.  Lists longer than
+ * 512 entries are split into several launches.  Nothing is allocated or copied: the list travels
+ * as a kernel parameter.  No reference counterpart (see sfc_classify). */
+typedef struct sfc_batch {
+    const void* hdr;         /* n x 64 B */
+    const uint16_t* in_port; /* n x u16 */
+    uint64_t* result;        /* n x u64 */
+    uint32_t n;              /* packets; 0 = skip */
+    uint32_t reserved;
+} sfc_batch;
+int sfc_classify_batches(sfc_handle* h, const sfc_batch* batches, uint32_t n_batches, uint32_t flags,
+                         void* cuda_stream);
+
 /* Same, with HOST buffers (pageable or pinned): the library stages them through device memory it
  * owns, runs the kernel and copies the results back before returning.  This is the call a host
  * dataplane shim (cgo) makes per batch. */
