@@ -14,7 +14,7 @@ import numpy as np
 
 from . import consts
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb200sfc.so")
+LIB_PATH = os.environ.get("B200SFC_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb200sfc.so")
 
 FLOW_KEY_DTYPE = np.dtype(
     [("src", "u1", 16), ("dst", "u1", 16), ("sport", "<u2"), ("dport", "<u2"), ("vlan", "<u2"), ("proto", "u1"),

@@ -22,6 +22,10 @@ using namespace sfc;
 
 namespace {
 constexpr int kTile = 256;
+#ifndef SFC_TILE_ACL
+#define SFC_TILE_ACL 256
+#endif
+constexpr int kTileAcl = SFC_TILE_ACL;
 constexpr int kStages = 2;
 constexpr int kTicketRing = 32;      // a launch uses slot seq % 32; slots are 32 bytes apart and self-resetting
 constexpr int kTicketStride = 8;     // u32 words per slot: {draw counter, finished producers, pad}
@@ -136,10 +140,12 @@ void fill_tables(DevTables& T, const ImageHeader& H, const uint8_t* b, unsigned 
     T.lpm4_root = (const uint32_t*)(b + H.lpm4_root_off);
     T.lpm4_nodes = (const uint32_t*)(b + H.lpm4_nodes_off);
     T.lpm4_nh = (const LpmRes*)(b + H.lpm4_nh_off);
+    T.lpm4_tails = (const LpmTail*)(b + H.lpm4_tail_off);
     T.lpm4_count = H.lpm4_count;
     T.lpm6_root = (const uint32_t*)(b + H.lpm6_root_off);
     T.lpm6_nodes = (const uint32_t*)(b + H.lpm6_nodes_off);
     T.lpm6_nh = (const LpmRes*)(b + H.lpm6_nh_off);
+    T.lpm6_tails = (const LpmTail*)(b + H.lpm6_tail_off);
     T.lpm6_count = H.lpm6_count;
     T.acl_nodes = (const unsigned long long*)(b + H.acl_nodes_off);
     T.acl_leaves = (const uint16_t*)(b + H.acl_leaf_off);
@@ -289,9 +295,9 @@ int launch_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uin
         SFC_TUNE_CASE(12, 768, 2)
 #undef SFC_TUNE_CASE
     }
-    if (c && a) return launch_variant<kTile, kStages, true, true>(h, 3, hdr, in_port, result, n, flags, st);
+    if (c && a) return launch_variant<kTileAcl, kStages, true, true>(h, 3, hdr, in_port, result, n, flags, st);
     if (c) return launch_variant<kTile, kStages, true, false>(h, 2, hdr, in_port, result, n, flags, st);
-    if (a) return launch_variant<kTile, kStages, false, true>(h, 1, hdr, in_port, result, n, flags, st);
+    if (a) return launch_variant<kTileAcl, kStages, false, true>(h, 1, hdr, in_port, result, n, flags, st);
     return launch_variant<kTile, kStages, false, false>(h, 0, hdr, in_port, result, n, flags, st);
 }
 
@@ -322,7 +328,7 @@ __global__ void gen_kernel(sfc_gen_spec spec, uint64_t first, uint64_t n, uint8_
 // =================================================================== life cycle ==========
 extern "C" {
 
-const char* sfc_version(void) { return "b200sfc 0.4 (image v7)"; }
+const char* sfc_version(void) { return "b200sfc 0.5 (image v8)"; }
 
 int sfc_create(int device_ordinal, sfc_handle** out) {
     if (!out) return -EINVAL;

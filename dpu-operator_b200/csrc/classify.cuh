@@ -33,10 +33,12 @@ struct DevTables {
     const uint32_t* lpm4_root;
     const uint32_t* lpm4_nodes;
     const LpmRes* lpm4_nh;
+    const LpmTail* lpm4_tails;
     uint32_t lpm4_count;
     const uint32_t* lpm6_root;
     const uint32_t* lpm6_nodes;
     const LpmRes* lpm6_nh;
+    const LpmTail* lpm6_tails;
     uint32_t lpm6_count;
     const unsigned long long* acl_nodes;  // kAclNodeEntries per node
     const uint16_t* acl_leaves;           // count, then rank | need flags, ranks ascending
@@ -300,9 +302,13 @@ __device__ __forceinline__ bool flow6_lookup(const DevTables& T, const Key& k, u
 }
 
 // ------------------------------------------------------------------ stage 4: LPM ---------
+__device__ __forceinline__ uint32_t lpm_word_mask(uint32_t len, int i) {  // bits of word i covered by /len
+    const int bits = (int)len - 32 * i;
+    return bits <= 0 ? 0u : (bits >= 32 ? 0xFFFFFFFFu : ~(0xFFFFFFFFu >> bits));
+}
 template <int MAX_BITS>
 __device__ __forceinline__ uint32_t lpm_lookup(const uint32_t* __restrict__ root, const uint32_t* __restrict__ nodes,
-                                               const uint32_t* a) {
+                                               const LpmTail* __restrict__ tails, const uint32_t* a) {
     uint32_t e = __ldg(root + (a[0] >> 16));
 #pragma unroll
     for (int pos = 16; pos < MAX_BITS; pos += 8) {  // static positions: the address stays in registers
@@ -310,7 +316,18 @@ __device__ __forceinline__ uint32_t lpm_lookup(const uint32_t* __restrict__ root
         uint32_t byte = (a[pos >> 5] >> (24 - (pos & 31))) & 0xFFu;
         e = __ldg(nodes + (size_t)(e & ~kLpmChild) * 256 + byte);
     }
-    return (e & kLpmChild) ? 0u : e;
+    if (e & kLpmChild) return 0u;
+    if (e & kLpmTail) {  // a lone prefix below this point: one record, one masked compare
+        uint32_t t[8];
+        ldg256(tails + (e & ~kLpmTail), t);
+        uint32_t d = (a[0] ^ t[0]) & lpm_word_mask(t[4], 0);
+        if (MAX_BITS > 32) {
+#pragma unroll
+            for (int i = 1; i < 4; ++i) d |= (a[i] ^ t[i]) & lpm_word_mask(t[4], i);
+        }
+        e = d ? t[6] : t[5];
+    }
+    return e;
 }
 
 // ------------------------------------------------------------------ the kernel -----------
@@ -326,7 +343,10 @@ template <int TILE, int STAGES, bool COUNTERS, bool ACL, bool MULTI = false>
 #ifndef SFC_MINB
 #define SFC_MINB 1
 #endif
-__global__ void __launch_bounds__(TILE + 32, SFC_MINB) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
+#ifndef SFC_MINB_ACL
+#define SFC_MINB_ACL 4  // <= 56 registers: four 288-thread CTAs per SM (cfg4: 67 vs 76 us per Mi packets; 5 would spill)
+#endif
+__global__ void __launch_bounds__(TILE + 32, ACL ? SFC_MINB_ACL : SFC_MINB) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
                                                               const uint16_t* __restrict__ in_port,
                                                               uint64_t* __restrict__ result, uint32_t n,
                                                               uint32_t n_tiles, uint32_t* ticket,
@@ -595,14 +615,14 @@ __global__ void __launch_bounds__(TILE + 32, SFC_MINB) classify_kernel(const __g
         // ---- stage 4: LPM on the destination ----
         if (!done && is_ip) {
             if (k.ip_ver == 4 && T.lpm4_count) {
-                uint32_t e = lpm_lookup<32>(T.lpm4_root, T.lpm4_nodes, k.dip);
+                uint32_t e = lpm_lookup<32>(T.lpm4_root, T.lpm4_nodes, T.lpm4_tails, k.dip);
                 if (e) {
                     uint2 r = __ldg(reinterpret_cast<const uint2*>(T.lpm4_nh + (e - 1)));
                     rhi = r.x;
                     rlo = r.y;
                 }
             } else if (k.ip_ver == 6 && T.lpm6_count) {
-                uint32_t e = lpm_lookup<128>(T.lpm6_root, T.lpm6_nodes, k.dip);
+                uint32_t e = lpm_lookup<128>(T.lpm6_root, T.lpm6_nodes, T.lpm6_tails, k.dip);
                 if (e) {
                     uint2 r = __ldg(reinterpret_cast<const uint2*>(T.lpm6_nh + (e - 1)));
                     rhi = r.x;

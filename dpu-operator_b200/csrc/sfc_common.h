@@ -124,6 +124,17 @@ struct LpmRes {
 // Leaf-pushed multibit trie: root indexed by the top 16 address bits, then 8-bit strides.
 // entry: bit31 set -> child node number in bits[0:31); else prefix_id+1 (0 = no prefix).
 constexpr uint32_t kLpmChild = 0x80000000u;
+// A sub-trie that holds a single prefix is not expanded into 256-entry nodes: the slot points at one
+// 32-byte record instead, and the lookup ends there with one masked compare.
+constexpr uint32_t kLpmTail = 0x40000000u;
+struct LpmTail {
+    uint32_t w[4];      // the prefix, masked to its length
+    uint32_t len;       // 1..128
+    uint32_t match;     // entry value (next-hop index + 1) if the address is inside the prefix
+    uint32_t fallback;  // entry value of the covering shorter prefix otherwise (0 = none)
+    uint32_t pad;
+};
+static_assert(sizeof(LpmTail) == 32, "one sector");
 
 // ---------------------------------------------------------------- ACL --------------------
 // Canonical key bytes K[0..43]; byte i = (Q[i>>2] >> (24 - 8*(i&3))) & 0xFF with
@@ -151,7 +162,7 @@ constexpr uint16_t kAclNeedG1 = 1u << 12, kAclNeedG2 = 1u << 13, kAclRankMask = 
 
 // ---------------------------------------------------------------- image ------------------
 constexpr uint64_t kImageMagic = 0x3130434653303042ull;  // "B00SFC01"
-constexpr uint32_t kImageVersion = 7;
+constexpr uint32_t kImageVersion = 8;
 constexpr size_t kImageAlign = 256;
 
 struct ImageHeader {
@@ -183,6 +194,9 @@ struct ImageHeader {
     uint64_t acl_nodes_off, acl_leaf_off, acl_rule_off, acl_res_off;
     uint32_t acl_nrules, acl_nnodes, acl_nleafwords, acl_ntrees;
     uint64_t acl_roots[kAclMaxTrees];  // node entries (see kAclLeaf)
+
+    uint64_t lpm4_tail_off, lpm6_tail_off;  // LpmTail records
+    uint32_t lpm4_ntails, lpm6_ntails;
 };
 static_assert(sizeof(ImageHeader) <= 512, "image header grew past its reserved 512 bytes");
 constexpr size_t kImageHeaderBytes = 512;

@@ -315,53 +315,70 @@ inline uint32_t addr_bits(const uint32_t* w, int pos, int n) {  // n <= 16, MSB-
     return (uint32_t)(two >> sh) & ((1u << n) - 1u);
 }
 
+// 16-8-8-... multibit trie with leaf pushing, built top-down from the prefix set so that a sub-trie
+// holding one single prefix becomes an LpmTail record instead of a chain of 256-entry nodes (random
+// IPv6 /48-/64 prefixes would otherwise cost six dependent loads and 6 KB each).
 struct Trie {
+    struct P {
+        const uint32_t* w;
+        int len;
+        uint32_t val;
+    };
     std::vector<uint32_t> root = std::vector<uint32_t>(65536, 0);
     std::vector<uint32_t> nodes;  // 256 entries per node
+    std::vector<LpmTail> tails;
 
-    void fill(std::vector<uint32_t>& arr, size_t idx, uint32_t val) {
-        uint32_t e = arr[idx];
-        if (e & kLpmChild) {
-            size_t base = (size_t)(e & ~kLpmChild) * 256;
-            for (int i = 0; i < 256; ++i) fill(nodes, base + i, val);
-        } else {
-            arr[idx] = val;
+    // the entry for a slot whose path is decided through `pos` bits; every prefix of S is longer than pos
+    // and lies on that path; F is what the slot inherits from shorter prefixes.  S is sorted by length.
+    uint32_t subtree(const std::vector<P>& S, int pos, uint32_t F) {
+        if (S.empty()) return F;
+        if (S.size() == 1) {
+            LpmTail t;
+            memset(&t, 0, sizeof(t));
+            for (int i = 0; i < 4; ++i) {
+                int bits = S[0].len - 32 * i;
+                t.w[i] = bits <= 0 ? 0u : (bits >= 32 ? S[0].w[i] : (S[0].w[i] & ~((1u << (32 - bits)) - 1u)));
+            }
+            t.len = (uint32_t)S[0].len;
+            t.match = S[0].val;
+            t.fallback = F;
+            tails.push_back(t);
+            return kLpmTail | (uint32_t)(tails.size() - 1);
         }
+        const size_t me = nodes.size() / 256;
+        nodes.resize(nodes.size() + 256, F);
+        std::map<uint32_t, std::vector<P>> deeper;
+        for (const P& p : S) {  // ascending length: longer prefixes overwrite shorter ones
+            if (p.len <= pos + 8) {
+                int free_bits = pos + 8 - p.len;
+                uint32_t first = addr_bits(p.w, pos, 8) & ~((1u << free_bits) - 1u);
+                for (uint32_t i = 0; i < (1u << free_bits); ++i) nodes[me * 256 + first + i] = p.val;
+            } else {
+                deeper[addr_bits(p.w, pos, 8)].push_back(p);
+            }
+        }
+        for (auto& kv : deeper) {
+            uint32_t e = subtree(kv.second, pos + 8, nodes[me * 256 + kv.first]);
+            nodes[me * 256 + kv.first] = e;
+        }
+        return kLpmChild | (uint32_t)me;
     }
-    // make sure arr[idx] is a child pointer; returns child number
-    uint32_t ensure_child(bool in_root, size_t idx) {
-        uint32_t e = in_root ? root[idx] : nodes[idx];
-        if (e & kLpmChild) return e & ~kLpmChild;
-        uint32_t child = (uint32_t)(nodes.size() / 256);
-        nodes.resize(nodes.size() + 256, e);  // leaf push: inherit the covering prefix
-        (in_root ? root[idx] : nodes[idx]) = kLpmChild | child;
-        return child;
-    }
-    void insert(const uint32_t* w, int len, uint32_t val) {
-        if (len <= 16) {
-            uint32_t first = len ? (addr_bits(w, 0, 16) & ~((1u << (16 - len)) - 1u)) : 0u;
-            uint32_t cnt = 1u << (16 - len);
-            for (uint32_t i = 0; i < cnt; ++i) fill(root, first + i, val);
-            return;
+    void build(const std::vector<P>& all) {  // sorted by length
+        std::map<uint32_t, std::vector<P>> deeper;
+        for (const P& p : all) {
+            if (p.len <= 16) {
+                uint32_t first = p.len ? (addr_bits(p.w, 0, 16) & ~((1u << (16 - p.len)) - 1u)) : 0u;
+                for (uint32_t i = 0; i < (1u << (16 - p.len)); ++i) root[first + i] = p.val;
+            } else {
+                deeper[addr_bits(p.w, 0, 16)].push_back(p);
+            }
         }
-        bool in_root = true;
-        size_t idx = addr_bits(w, 0, 16);
-        int consumed = 16;
-        while (len > consumed + 8) {
-            uint32_t child = ensure_child(in_root, idx);
-            idx = (size_t)child * 256 + addr_bits(w, consumed, 8);
-            in_root = false;
-            consumed += 8;
-        }
-        uint32_t child = ensure_child(in_root, idx);
-        int free_bits = consumed + 8 - len;
-        uint32_t first = addr_bits(w, consumed, 8) & ~((1u << free_bits) - 1u);
-        for (uint32_t i = 0; i < (1u << free_bits); ++i) fill(nodes, (size_t)child * 256 + first + i, val);
+        for (auto& kv : deeper) root[kv.first] = subtree(kv.second, 16, root[kv.first]);
     }
 };
 
 void build_lpm(Blob& blob, const RuleStore& rs, int af, const std::map<RuleStore::LpmKey, LpmRec>& recs_map, uint64_t& root_off, uint64_t& nodes_off,
-               uint64_t& nh_off, uint32_t& nnodes, uint32_t& count) {
+               uint64_t& nh_off, uint32_t& nnodes, uint32_t& count, uint64_t& tail_off, uint32_t& ntails) {
     std::vector<const LpmRec*> sorted;
     std::vector<LpmRec> recs;
     recs.reserve(recs_map.size());
@@ -372,16 +389,22 @@ void build_lpm(Blob& blob, const RuleStore& rs, int af, const std::map<RuleStore
                      [](const LpmRec* a, const LpmRec* b) { return a->len < b->len; });
     Trie t;
     uint32_t max_id = 0;
+    std::vector<Trie::P> all;
+    all.reserve(sorted.size());
     for (auto* r : sorted) {
-        t.insert(r->w, r->len, r->id + 1);
+        all.push_back({r->w, r->len, r->id + 1});
         max_id = std::max(max_id, r->id);
     }
+    t.build(all);
     count = (uint32_t)recs.size();
     nnodes = (uint32_t)(t.nodes.size() / 256);
     root_off = blob.reserve(65536 * 4, 0);
     memcpy(blob.at<uint8_t>(root_off), t.root.data(), 65536 * 4);
     nodes_off = blob.reserve(std::max<size_t>(t.nodes.size() * 4, 4), 0);
     if (!t.nodes.empty()) memcpy(blob.at<uint8_t>(nodes_off), t.nodes.data(), t.nodes.size() * 4);
+    ntails = (uint32_t)t.tails.size();
+    tail_off = blob.reserve(std::max<size_t>(t.tails.size() * sizeof(LpmTail), 32), 0);
+    if (!t.tails.empty()) memcpy(blob.at<uint8_t>(tail_off), t.tails.data(), t.tails.size() * sizeof(LpmTail));
     size_t nh_n = recs.empty() ? 1 : (size_t)max_id + 1;
     nh_off = blob.reserve(nh_n * sizeof(LpmRes), 0);
     for (auto& r : recs) {
@@ -709,8 +732,10 @@ bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& imag
             w[kv.first].res_lo = res_lo(SFC_STAGE_L2_WILD, kv.second->id);
         }
     }
-    build_lpm(blob, rs, 4, rs.lpm4, H.lpm4_root_off, H.lpm4_nodes_off, H.lpm4_nh_off, H.lpm4_nnodes, H.lpm4_count);
-    build_lpm(blob, rs, 6, rs.lpm6, H.lpm6_root_off, H.lpm6_nodes_off, H.lpm6_nh_off, H.lpm6_nnodes, H.lpm6_count);
+    build_lpm(blob, rs, 4, rs.lpm4, H.lpm4_root_off, H.lpm4_nodes_off, H.lpm4_nh_off, H.lpm4_nnodes, H.lpm4_count,
+              H.lpm4_tail_off, H.lpm4_ntails);
+    build_lpm(blob, rs, 6, rs.lpm6, H.lpm6_root_off, H.lpm6_nodes_off, H.lpm6_nh_off, H.lpm6_nnodes, H.lpm6_count,
+              H.lpm6_tail_off, H.lpm6_ntails);
     build_acl(blob, rs.acl, H);
 
     size_t total = (image.size() + kImageAlign - 1) / kImageAlign * kImageAlign;
@@ -734,7 +759,9 @@ const char* validate_image(const uint8_t* img, size_t len) {
               ((H.l2x_mask & (H.l2x_mask + 1)) == 0) && inside(H.l2w_off, (uint64_t)H.l2w_n * sizeof(L2Wild)) &&
               inside(H.lpm4_root_off, 65536 * 4) && inside(H.lpm4_nodes_off, (uint64_t)H.lpm4_nnodes * 1024) &&
               inside(H.lpm6_root_off, 65536 * 4) && inside(H.lpm6_nodes_off, (uint64_t)H.lpm6_nnodes * 1024) &&
-              inside(H.lpm4_nh_off, 8) && inside(H.lpm6_nh_off, 8) && H.flow4_nhash >= 1 &&
+              inside(H.lpm4_nh_off, 8) && inside(H.lpm6_nh_off, 8) &&
+              inside(H.lpm4_tail_off, std::max<uint64_t>((uint64_t)H.lpm4_ntails * sizeof(LpmTail), 32)) &&
+              inside(H.lpm6_tail_off, std::max<uint64_t>((uint64_t)H.lpm6_ntails * sizeof(LpmTail), 32)) && H.flow4_nhash >= 1 &&
               H.flow4_nhash <= kMaxHashes && H.flow6_nhash >= 1 && H.flow6_nhash <= kMaxHashes && H.flow4_nbuckets &&
               H.flow6_nbuckets && H.acl_nrules <= SFC_MAX_ACL_RULES && H.acl_ntrees <= kAclMaxTrees;
     if (ok && H.acl_nrules)

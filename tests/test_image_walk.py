@@ -26,13 +26,13 @@ def expand_seed(seed, n):
 
 
 class Image:
-    """Field offsets follow struct ImageHeader (version 7)."""
+    """Field offsets follow struct ImageHeader (version 8)."""
 
     def __init__(self, img: np.ndarray):
         self.b = img.tobytes()
         u = lambda fmt, off: struct.unpack_from("<" + fmt, self.b, off)  # noqa: E731
         magic, ver, hb, total, epoch = u("QIIQQ", 0)
-        assert magic == 0x3130434653303042 and ver == 7 and hb == 512 and total == len(self.b)
+        assert magic == 0x3130434653303042 and ver == 8 and hb == 512 and total == len(self.b)
         o = 32
         self.f4_off, self.f4_seed, self.f4_nb, self.f4_nh, self.f4_cnt, self.f4_first = u("QQIIII", o); o += 32
         self.f6_off, self.f6_seed, self.f6_nb, self.f6_nh, self.f6_cnt, self.f6_first = u("QQIIII", o); o += 32
@@ -41,7 +41,8 @@ class Image:
         self.lpm6 = u("QQQII", o); o += 32
         self.acl_nodes_off, self.acl_leaf_off, self.acl_rule_off, self.acl_res_off = u("QQQQ", o); o += 32
         self.acl_nrules, self.acl_nnodes, self.acl_nleaf, self.acl_ntrees = u("IIII", o); o += 16
-        self.acl_roots = u("8Q", o)
+        self.acl_roots = u("8Q", o); o += 64
+        self.lpm4_tail_off, self.lpm6_tail_off, self.lpm4_ntails, self.lpm6_ntails = u("QQII", o)
 
     def u32(self, off, n):
         return np.frombuffer(self.b, dtype="<u4", count=n, offset=off)
@@ -90,7 +91,17 @@ class Image:
             byte = (addr_words[pos >> 5] >> (24 - (pos & 31))) & 0xFF
             e = int(self.u32(nodes_off + ((e & 0x7FFFFFFF) * 256 + byte) * 4, 1)[0])
             pos += 8
-        if e & 0x80000000 or e == 0:
+        if e & 0x80000000:
+            return None
+        if e & 0x40000000:  # a lone prefix: one record, one masked compare
+            rec = self.u32((self.lpm4_tail_off if af == 4 else self.lpm6_tail_off) + (e & 0x3FFFFFFF) * 32, 8)
+            ln, diff = int(rec[4]), 0
+            for i in range(4):
+                bits = min(32, max(0, ln - 32 * i))
+                mask = (0xFFFFFFFF << (32 - bits)) & 0xFFFFFFFF if bits else 0
+                diff |= (addr_words[i] ^ int(rec[i])) & mask
+            e = int(rec[6]) if diff else int(rec[5])
+        if e == 0:
             return None
         hi, lo = self.u32(nh_off + (e - 1) * 8, 2)
         return (int(hi) << 32) | int(lo)
