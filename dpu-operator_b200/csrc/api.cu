@@ -22,11 +22,20 @@ using namespace sfc;
 
 namespace {
 constexpr int kTile = 256;
+constexpr int kStages = 2;
 #ifndef SFC_TILE_ACL
 #define SFC_TILE_ACL 256
 #endif
 constexpr int kTileAcl = SFC_TILE_ACL;
-constexpr int kStages = 2;
+#ifndef SFC_STAGES_ACL
+#define SFC_STAGES_ACL 1
+#endif
+// The ACL variants are bound by table latency, not by the packet stream: one stage is enough (a slot is
+// released as soon as its records sit in registers) and the shared memory it frees becomes L1 for the
+// tree nodes and rule records (configs[3]: 63 -> 58 us per Mi packets).
+constexpr int kStagesAcl = SFC_STAGES_ACL;
+template <bool A>
+constexpr int stages_for() { return A ? kStagesAcl : kStages; }
 constexpr int kTicketRing = 32;      // a launch uses slot seq % 32; slots are 32 bytes apart and self-resetting
 constexpr int kTicketStride = 8;     // u32 words per slot: {draw counter, finished producers, pad}
 constexpr size_t kHostChunk = 1u << 18;  // packets per pipelined chunk in sfc_classify_host
@@ -147,12 +156,13 @@ void fill_tables(DevTables& T, const ImageHeader& H, const uint8_t* b, unsigned 
     T.lpm6_nh = (const LpmRes*)(b + H.lpm6_nh_off);
     T.lpm6_tails = (const LpmTail*)(b + H.lpm6_tail_off);
     T.lpm6_count = H.lpm6_count;
-    T.acl_nodes = (const unsigned long long*)(b + H.acl_nodes_off);
+    T.acl_nodes = (const uint4*)(b + H.acl_nodes_off);
     T.acl_leaves = (const uint16_t*)(b + H.acl_leaf_off);
     T.acl_rules = (const uint32_t*)(b + H.acl_rule_off);
     T.acl_res = (const uint32_t*)(b + H.acl_res_off);
     T.acl_nrules = H.acl_nrules;
     T.acl_ntrees = H.acl_ntrees;
+    static_assert(sizeof(T.acl_roots) == sizeof(H.acl_roots), "root entries are copied verbatim");
     memcpy(T.acl_roots, H.acl_roots, sizeof(T.acl_roots));
     T.counters = counters;
 }
@@ -237,8 +247,8 @@ int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_
 template <bool C, bool A>
 int launch_multi(sfc_handle* h, int slot, const BatchList& L, uint64_t rows, uint32_t n_tiles, uint32_t flags,
                  cudaStream_t st) {
-    auto kern = classify_kernel<kTile, kStages, C, A, true>;
-    constexpr int smem = SmemLayout<kTile, kStages, A>::kBytes;
+    auto kern = classify_kernel<kTile, stages_for<A>(), C, A, true>;
+    constexpr int smem = SmemLayout<kTile, stages_for<A>(), A>::kBytes;
     if (!h->ctas_per_sm[slot]) {
         CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         int per = 0;
@@ -295,9 +305,9 @@ int launch_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uin
         SFC_TUNE_CASE(12, 768, 2)
 #undef SFC_TUNE_CASE
     }
-    if (c && a) return launch_variant<kTileAcl, kStages, true, true>(h, 3, hdr, in_port, result, n, flags, st);
+    if (c && a) return launch_variant<kTileAcl, kStagesAcl, true, true>(h, 3, hdr, in_port, result, n, flags, st);
     if (c) return launch_variant<kTile, kStages, true, false>(h, 2, hdr, in_port, result, n, flags, st);
-    if (a) return launch_variant<kTileAcl, kStages, false, true>(h, 1, hdr, in_port, result, n, flags, st);
+    if (a) return launch_variant<kTileAcl, kStagesAcl, false, true>(h, 1, hdr, in_port, result, n, flags, st);
     return launch_variant<kTile, kStages, false, false>(h, 0, hdr, in_port, result, n, flags, st);
 }
 
@@ -328,7 +338,7 @@ __global__ void gen_kernel(sfc_gen_spec spec, uint64_t first, uint64_t n, uint8_
 // =================================================================== life cycle ==========
 extern "C" {
 
-const char* sfc_version(void) { return "b200sfc 0.5 (image v8)"; }
+const char* sfc_version(void) { return "b200sfc 0.6 (image v9)"; }
 
 int sfc_create(int device_ordinal, sfc_handle** out) {
     if (!out) return -EINVAL;
@@ -1113,8 +1123,8 @@ int static_setup(int device, StaticDev& d, char* errbuf, size_t errlen) {
         return static_fail(errbuf, errlen, -ENOSYS, "driver lacks cuTensorMapEncodeTiled");
     d.encode = (EncodeTiledFn)fn;
     const void* kerns[2] = {(const void*)classify_kernel<kTile, kStages, false, false>,
-                            (const void*)classify_kernel<kTile, kStages, false, true>};
-    const int smem[2] = {SmemLayout<kTile, kStages, false>::kBytes, SmemLayout<kTile, kStages, true>::kBytes};
+                            (const void*)classify_kernel<kTile, kStagesAcl, false, true>};
+    const int smem[2] = {SmemLayout<kTile, kStages, false>::kBytes, SmemLayout<kTile, kStagesAcl, true>::kBytes};
     for (int v = 0; v < 2; ++v) {
         e = cudaFuncSetAttribute(kerns[v], cudaFuncAttributeMaxDynamicSharedMemorySize, smem[v]);
         if (e == cudaSuccess)
@@ -1187,7 +1197,7 @@ extern "C" int sfc_classify_static(int device, const void* image_host, size_t im
     const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)d.sm_count * d.ctas_per_sm[acl ? 1 : 0]);
     uint32_t* ticket = (uint32_t*)d.area;  // {draw counter, finished producers}: cleared above, reset by the kernel too
     if (acl)
-        classify_kernel<kTile, kStages, false, true><<<grid, kTile + 32, SmemLayout<kTile, kStages, true>::kBytes, st>>>(
+        classify_kernel<kTile, kStagesAcl, false, true><<<grid, kTile + 32, SmemLayout<kTile, kStagesAcl, true>::kBytes, st>>>(
             map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, 0u, T, NoBatches{});
     else
         classify_kernel<kTile, kStages, false, false><<<grid, kTile + 32, SmemLayout<kTile, kStages, false>::kBytes, st>>>(

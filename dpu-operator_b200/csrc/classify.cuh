@@ -40,12 +40,12 @@ struct DevTables {
     const LpmRes* lpm6_nh;
     const LpmTail* lpm6_tails;
     uint32_t lpm6_count;
-    const unsigned long long* acl_nodes;  // kAclNodeEntries per node
-    const uint16_t* acl_leaves;           // count, then rank | need flags, ranks ascending
+    const uint4* acl_nodes;               // AclEntry arrays, 2^bits per node
+    const uint16_t* acl_leaves;           // overflow candidate lists
     const uint32_t* acl_rules;            // kAclRuleWords per rank: groups G0, G1, G2
     const uint32_t* acl_res;              // per rank: rule id | deny << 31
     uint32_t acl_nrules, acl_ntrees;
-    unsigned long long acl_roots[kAclMaxTrees];
+    uint4 acl_roots[kAclMaxTrees];
     unsigned long long* counters;
 };
 
@@ -149,6 +149,12 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
     asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
     return v;
 }
+// one key bit of the ACL stage: `field` = row offset | right shift (see sfc_common.h), appended to idx
+__device__ __forceinline__ uint32_t acl_key_bit(uint32_t key_base, uint32_t field, uint32_t idx) {
+    uint32_t word;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(word) : "r"(key_base + (field & 0xFF80u)));
+    return (idx << 1) | ((word >> (field & 31u)) & 1u);
+}
 // one 32-byte sector, read-only path
 __device__ __forceinline__ void ldg256(const void* p, uint32_t* r) {
     asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -158,6 +164,13 @@ __device__ __forceinline__ void ldg256(const void* p, uint32_t* r) {
 // same sector, allowed to stay in L1 (tables small enough to live there)
 __device__ __forceinline__ void ldg256_l1(const void* p, uint32_t* r) {
     asm volatile("ld.global.nc.L1::evict_last.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "l"(p));
+}
+// same sector through L1 with the default policy: the ACL rule records (96 B each) are few and hot;
+// on B200 letting them live in L1 took configs[3] from 58 to 46 us per Mi packets
+__device__ __forceinline__ void ldg256_c(const void* p, uint32_t* r) {
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "l"(p));
 }
@@ -334,7 +347,7 @@ __device__ __forceinline__ uint32_t lpm_lookup(const uint32_t* __restrict__ root
 template <int TILE, int STAGES, bool ACL>
 struct SmemLayout {
     static constexpr int kTileBytes = TILE * 64;
-    static constexpr int kAclBytes = ACL ? (TILE / 32) * kAclKeyWords * 32 * 4 : 0;
+    static constexpr int kAclBytes = ACL ? (TILE / 32) * kAclKeyRows * 32 * 4 : 0;
     static constexpr int kBytes = STAGES * kTileBytes + kAclBytes + 2 * STAGES * 8 + 16 * 8 + 32 * 4 + STAGES * 4 + 16 +
                                   STAGES * (int)sizeof(StageInfo) + 1024;
 };
@@ -446,6 +459,7 @@ __global__ void __launch_bounds__(TILE + 32, ACL ? SFC_MINB_ACL : SFC_MINB) clas
     }
     // ---------------- consumers: one packet per thread per tile ----------------
     const int lane = tid & 31;
+    if (ACL) aclq[(tid >> 5) * (kAclKeyRows * 32) + 11 * 32 + lane] = 0u;  // the zero row unused tree bits read
     const uint32_t row_off = (uint32_t)tid * 64u;
     const uint32_t sw = ((uint32_t)tid >> 1) & 3u;
     for (uint32_t it = 0;; ++it) {
@@ -501,57 +515,92 @@ __global__ void __launch_bounds__(TILE + 32, ACL ? SFC_MINB_ACL : SFC_MINB) clas
         bool done = !live;  // lanes past the end of the batch hold zero-filled records
 
         // ---- stage 1: ACL — bit-selecting decision trees, one packet per thread ----
-        // Each tree narrows the candidates to a short leaf list in rank order; the first rule of a leaf
-        // that matches all 11 key words under its mask wins, and the best rank over the trees is the
+        // Each tree narrows the candidates to a short list in rank order; the first candidate that
+        // matches all 11 key words under its mask wins, and the best rank over the trees is the
         // verdict.  The key words sit in shared memory because the tested bit positions are table data.
         if (ACL) {
-            uint32_t* q = aclq + (tid >> 5) * (kAclKeyWords * 32) + lane;
-            q[0 * 32] = (port << 16) | (k.meta >> 8);
-            q[1 * 32] = (k.ip_ver << 24) | ((k.meta & 0xFFu) << 16) | (k.ports >> 16);
-            q[2 * 32] = k.ports << 16;
+            uint32_t* q = aclq + (tid >> 5) * (kAclKeyRows * 32) + lane;
+            const uint32_t q0 = (port << 16) | (k.meta >> 8);
+            const uint32_t q1 = (k.ip_ver << 24) | ((k.meta & 0xFFu) << 16) | (k.ports >> 16), q2 = k.ports << 16;
+            q[0 * 32] = q0;
+            q[1 * 32] = q1;
+            q[2 * 32] = q2;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 q[(3 + i) * 32] = k.sip[i];
                 q[(7 + i) * 32] = k.dip[i];
             }
             if (live && is_ip) {
-                // key words in registers for the rule compares (static indices); q[] only serves bit tests
-                const uint32_t q0 = (port << 16) | (k.meta >> 8);
-                const uint32_t q1 = (k.ip_ver << 24) | ((k.meta & 0xFFu) << 16) | (k.ports >> 16), q2 = k.ports << 16;
+                const uint32_t qb = smem_u32(q);
                 uint32_t best = 0xFFFFFFFFu;
-                for (uint32_t t = 0; t < T.acl_ntrees; ++t) {
-                    unsigned long long e = T.acl_roots[t];
-                    while (!(e & kAclLeaf)) {
-                        uint32_t idx = 0;
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const uint32_t pb = (uint32_t)(e >> (28 + 9 * j)) & kAclNoBit;
-                            if (pb != kAclNoBit) idx = (idx << 1) | ((q[(pb >> 5) * 32] >> (31 - (pb & 31))) & 1u);
-                        }
-                        e = __ldg(T.acl_nodes + (size_t)(e & kAclPtrMask) * kAclNodeEntries + idx);
+                // full compare of candidate c against the key held in registers; g = its G0 sector
+                auto matches = [&](uint32_t c, const uint32_t* g) -> bool {
+                    uint32_t d = ((q1 ^ g[0]) & g[4]) | ((q2 ^ g[1]) & g[5]) | ((k.dip[0] ^ g[2]) & g[6]) |
+                                 ((k.sip[0] ^ g[3]) & g[7]);
+                    if (d) return false;
+                    const uint32_t* rec = T.acl_rules + (size_t)(c & kAclRankMask) * kAclRuleWords;
+                    uint32_t h[8];
+                    if (c & kAclNeedG1) {
+                        ldg256_c(rec + 8, h);  // G1: words {0, 8, 9, 10}
+                        d = ((q0 ^ h[0]) & h[4]) | ((k.dip[1] ^ h[1]) & h[5]) | ((k.dip[2] ^ h[2]) & h[6]) |
+                            ((k.dip[3] ^ h[3]) & h[7]);
+                        if (d) return false;
                     }
-                    const uint16_t* leaf = T.acl_leaves + (e & kAclPtrMask);
-                    const uint32_t cnt = __ldg(leaf);
-                    for (uint32_t i = 1; i <= cnt; ++i) {
-                        const uint32_t le = __ldg(leaf + i), r = le & kAclRankMask;
-                        if (r >= best) break;  // ranks ascend: nothing better left in this leaf
-                        const uint32_t* rec = T.acl_rules + (size_t)r * kAclRuleWords;
-                        uint32_t g[8];
-                        ldg256(rec, g);  // G0: words {1, 2, 7, 3}
-                        uint32_t d = ((q1 ^ g[0]) & g[4]) | ((q2 ^ g[1]) & g[5]) | ((k.dip[0] ^ g[2]) & g[6]) |
-                                     ((k.sip[0] ^ g[3]) & g[7]);
-                        if (d == 0u && (le & kAclNeedG1)) {
-                            ldg256(rec + 8, g);  // G1: words {0, 8, 9, 10}
-                            d = ((q0 ^ g[0]) & g[4]) | ((k.dip[1] ^ g[1]) & g[5]) | ((k.dip[2] ^ g[2]) & g[6]) |
-                                ((k.dip[3] ^ g[3]) & g[7]);
-                        }
-                        if (d == 0u && (le & kAclNeedG2)) {
-                            ldg256(rec + 16, g);  // G2: words {4, 5, 6}
-                            d = ((k.sip[1] ^ g[0]) & g[4]) | ((k.sip[2] ^ g[1]) & g[5]) | ((k.sip[3] ^ g[2]) & g[6]);
-                        }
-                        if (d == 0u) {
-                            best = r;
+                    if (c & kAclNeedG2) {
+                        ldg256_c(rec + 16, h);  // G2: words {4, 5, 6}
+                        d = ((k.sip[1] ^ h[0]) & h[4]) | ((k.sip[2] ^ h[1]) & h[5]) | ((k.sip[3] ^ h[2]) & h[6]);
+                    }
+                    return d == 0u;
+                };
+                for (uint32_t t = 0; t < T.acl_ntrees; ++t) {
+                    uint4 e = T.acl_roots[t];
+                    while (!(e.x & kAclLeafBit)) {  // one 16-byte load per level
+                        uint32_t idx = acl_key_bit(qb, e.y & 0xFFFFu, 0u);
+                        idx = acl_key_bit(qb, e.y >> 16, idx);
+                        idx = acl_key_bit(qb, e.z & 0xFFFFu, idx);
+                        idx = acl_key_bit(qb, e.z >> 16, idx);
+                        idx = acl_key_bit(qb, e.w & 0xFFFFu, idx);
+                        idx = acl_key_bit(qb, e.w >> 16, idx);
+                        e = __ldg(T.acl_nodes + (e.x + idx));
+                    }
+                    // the first six candidates travel in the entry itself; they are tried two at a time so
+                    // that the rule sectors of a pair are in flight together
+                    const uint32_t cw[3] = {e.y, e.z, e.w};
+                    bool open = true;  // false once this tree cannot improve `best` any more
+#pragma unroll
+                    for (int p = 0; p < 3; ++p) {
+                        if (!open) break;
+                        const uint32_t ca = cw[p] & 0xFFFFu, cb = cw[p] >> 16;
+                        if (ca == kAclNone || (ca & kAclRankMask) >= best) {
+                            open = false;
                             break;
+                        }
+                        const bool two = cb != kAclNone && (cb & kAclRankMask) < best;
+                        uint32_t ga[8], gb[8];
+                        ldg256_c(T.acl_rules + (size_t)(ca & kAclRankMask) * kAclRuleWords, ga);
+                        if (two) ldg256_c(T.acl_rules + (size_t)(cb & kAclRankMask) * kAclRuleWords, gb);
+                        if (matches(ca, ga)) {
+                            best = ca & kAclRankMask;
+                            open = false;
+                        } else if (!two) {
+                            open = false;
+                        } else if (matches(cb, gb)) {
+                            best = cb & kAclRankMask;
+                            open = false;
+                        }
+                    }
+                    if (open && (e.x & kAclMoreBit)) {  // rare: more than six candidates and none matched yet
+                        const uint16_t* more = T.acl_leaves + (e.x & kAclOffMask);
+                        const uint32_t cnt = __ldg(more);
+                        for (uint32_t i = 1; i <= cnt; ++i) {
+                            const uint32_t c = __ldg(more + i);
+                            if ((c & kAclRankMask) >= best) break;
+                            uint32_t g[8];
+                            ldg256_c(T.acl_rules + (size_t)(c & kAclRankMask) * kAclRuleWords, g);
+                            if (matches(c, g)) {
+                                best = c & kAclRankMask;
+                                break;
+                            }
                         }
                     }
                 }

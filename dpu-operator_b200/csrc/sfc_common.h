@@ -143,26 +143,36 @@ static_assert(sizeof(LpmTail) == 32, "one sector");
 constexpr int kAclKeyWords = 11;
 constexpr int kAclKeyBytes = 44;
 constexpr int kAclKeyBits = 352;
-// Decision-tree node: 16 child entries of 64 bits (one 128-byte line).  An entry carries the child
-// pointer AND the four bit positions the child tests, so a level costs one load:
-//   bits [0:27)  node index, or — if bit 27 (kAclLeaf) is set — offset into the leaf array
-//   bits [28:64) four 9-bit key-bit positions tested by that child (0x1FF = unused), first = MSB
-// Leaf array (u16): count, then entries rank | needG1 << 12 | needG2 << 13, ranks ascending.
+// Decision-tree entry: 16 bytes (one LDG.128).  An entry describes the CHILD it leads to, so a level
+// costs one load and the leaf list needs none for its first six candidates.
+//   inner  x = offset of the child's entry array (bit 31 clear); the child tests up to six key bits and
+//            has 2^bits entries; y, z, w hold six 16-bit fields, first = most significant index bit:
+//            field = key_word * 128 | right_shift  (128 = one row of the per-warp key array in shared
+//            memory, right_shift = 31 - bit position inside the word).  Unused fields name row 11,
+//            which holds zero, and come first — so the index stays below 2^bits without a branch.
+//   leaf   x = kAclLeafBit | (kAclMoreBit | offset into the overflow list, if more than six candidates);
+//            y, z, w = six u16 candidates rank | needG1 << 12 | needG2 << 13, ranks ascending,
+//            0xFFFF = none.
+// Overflow list (u16): count, then the candidates beyond the sixth.
 // Rule record (96 B, three 32-byte groups so the common case is ONE sector):
 //   G0 = value, mask of key words {1, 2, 7, 3}   (ip_ver/proto/sport, dport, dst[0], src[0])
 //   G1 = value, mask of key words {0, 8, 9, 10}  (in_port/vlan, dst[1..3])
 //   G2 = value of words {4, 5, 6}, pad, mask of words {4, 5, 6}, pad   (src[1..3])
-constexpr int kAclNodeEntries = 16;
+struct AclEntry {
+    uint32_t x, y, z, w;
+};
+constexpr int kAclMaxNodeBits = 6;
+constexpr int kAclInline = 6;
+constexpr int kAclKeyRows = 12;  // 11 key words + the zero row
+constexpr uint32_t kAclZeroField = 11u * 128u;
 constexpr int kAclRuleWords = 24;
 constexpr int kAclMaxTrees = 8;
-constexpr uint64_t kAclLeaf = 1ull << 27;
-constexpr uint64_t kAclPtrMask = (1ull << 27) - 1;
-constexpr uint32_t kAclNoBit = 0x1FFu;
-constexpr uint16_t kAclNeedG1 = 1u << 12, kAclNeedG2 = 1u << 13, kAclRankMask = 0x0FFFu;
+constexpr uint32_t kAclLeafBit = 0x80000000u, kAclMoreBit = 0x40000000u, kAclOffMask = 0x0FFFFFFFu;
+constexpr uint16_t kAclNeedG1 = 1u << 12, kAclNeedG2 = 1u << 13, kAclRankMask = 0x0FFFu, kAclNone = 0xFFFFu;
 
 // ---------------------------------------------------------------- image ------------------
 constexpr uint64_t kImageMagic = 0x3130434653303042ull;  // "B00SFC01"
-constexpr uint32_t kImageVersion = 8;
+constexpr uint32_t kImageVersion = 9;
 constexpr size_t kImageAlign = 256;
 
 struct ImageHeader {
@@ -192,8 +202,8 @@ struct ImageHeader {
 
     // ACL: a forest of bit-selecting decision trees over the 352-bit key, leaves scanned in rank order
     uint64_t acl_nodes_off, acl_leaf_off, acl_rule_off, acl_res_off;
-    uint32_t acl_nrules, acl_nnodes, acl_nleafwords, acl_ntrees;
-    uint64_t acl_roots[kAclMaxTrees];  // node entries (see kAclLeaf)
+    uint32_t acl_nrules, acl_nentries, acl_nleafwords, acl_ntrees;
+    AclEntry acl_roots[kAclMaxTrees];
 
     uint64_t lpm4_tail_off, lpm6_tail_off;  // LpmTail records
     uint32_t lpm4_ntails, lpm6_ntails;

@@ -420,7 +420,8 @@ void build_lpm(Blob& blob, const RuleStore& rs, int af, const std::map<RuleStore
 // goes to both children).  Rules are ranked by (priority desc, id asc); a leaf lists its candidate
 // rules in rank order and the kernel takes the first that matches in full, so the trees only ever
 // narrow the candidate set — a wrong cut can cost time, never correctness.
-//  * a node tests up to 4 bits (16 children), chosen greedily to minimise the largest child;
+//  * a node tests up to 6 bits (64 children; 5 or 4 when memory is short), chosen greedily to minimise
+//    the largest child;
 //  * below a rule that matches the whole subspace of a node nothing of lower rank can win: pruned;
 //  * identical sub-problems (same rule list) are built once and shared;
 //  * rules are first split into categories by which fields they leave (almost) open — destination,
@@ -457,37 +458,47 @@ void acl_key_words(const sfc_acl_rule& r, uint32_t* val, uint32_t* mask) {
 }
 
 struct AclBuilder {
-    static constexpr int kLeafMax = 8, kMaxDepth = 12, kBitsPerNode = 4;
+    static constexpr int kLeafMax = 8, kMaxDepth = 12;
     struct R {
         uint32_t val[kAclKeyWords], mask[kAclKeyWords];
     };
-    std::vector<R> rules;          // by rank
-    std::vector<uint64_t> nodes;   // kAclNodeEntries per node
-    std::vector<uint16_t> leaves;  // count, entries...
-    std::map<std::vector<uint16_t>, uint64_t> node_memo, leaf_memo;
+    int bits_per_node = 5;
+    std::vector<R> rules;           // by rank
+    std::vector<AclEntry> nodes;    // child arrays, 2^bits entries each
+    std::vector<uint16_t> leaves;   // overflow lists: count, candidates beyond the sixth
+    std::map<std::vector<uint16_t>, AclEntry> node_memo, leaf_memo;
     size_t budget_bytes = ~(size_t)0;
     bool over_budget = false;
 
     static bool bit(const uint32_t* w, int b) { return (w[b >> 5] >> (31 - (b & 31))) & 1u; }
-    size_t bytes() const { return nodes.size() * 8 + leaves.size() * 2; }
+    size_t bytes() const { return nodes.size() * sizeof(AclEntry) + leaves.size() * 2; }
 
-    uint16_t leaf_entry(uint16_t r) const {
+    uint16_t candidate(uint16_t r) const {
         const uint32_t* m = rules[r].mask;
         uint16_t e = r;
         if (m[0] | m[8] | m[9] | m[10]) e |= kAclNeedG1;
         if (m[4] | m[5] | m[6]) e |= kAclNeedG2;
         return e;
     }
-    uint64_t make_leaf(const std::vector<uint16_t>& rs) {
+    AclEntry make_leaf(const std::vector<uint16_t>& rs) {
         auto it = leaf_memo.find(rs);
         if (it != leaf_memo.end()) return it->second;
-        uint64_t off = leaves.size();
-        leaves.push_back((uint16_t)rs.size());
-        for (uint16_t r : rs) leaves.push_back(leaf_entry(r));
-        return leaf_memo[rs] = kAclLeaf | off | (~0ull << 28);
+        uint16_t c[kAclInline];
+        for (int i = 0; i < kAclInline; ++i) c[i] = i < (int)rs.size() ? candidate(rs[i]) : kAclNone;
+        AclEntry e;
+        e.x = kAclLeafBit;
+        if ((int)rs.size() > kAclInline) {
+            e.x |= kAclMoreBit | (uint32_t)leaves.size();
+            leaves.push_back((uint16_t)(rs.size() - kAclInline));
+            for (size_t i = kAclInline; i < rs.size(); ++i) leaves.push_back(candidate(rs[i]));
+        }
+        e.y = c[0] | (uint32_t)c[1] << 16;
+        e.z = c[2] | (uint32_t)c[3] << 16;
+        e.w = c[4] | (uint32_t)c[5] << 16;
+        return leaf_memo[rs] = e;
     }
 
-    uint64_t build(std::vector<uint16_t> rs, const uint32_t* fixed, int depth) {
+    AclEntry build(std::vector<uint16_t> rs, const uint32_t* fixed, int depth) {
         // prune everything ranked below the first rule that covers this node's whole subspace
         for (size_t i = 0; i < rs.size(); ++i) {
             bool covered = true;
@@ -516,10 +527,10 @@ struct AclBuilder {
         if (memo != node_memo.end()) return memo->second;
 
         std::vector<std::vector<uint16_t>> cells(1, rs);
-        int chosen[kBitsPerNode], nchosen = 0;
+        int chosen[kAclMaxNodeBits], nchosen = 0;
         std::vector<uint32_t> n0(kAclKeyBits), n1(kAclKeyBits), worst(kAclKeyBits);
         std::vector<uint8_t> progress(kAclKeyBits);
-        for (int j = 0; j < kBitsPerNode; ++j) {
+        for (int j = 0; j < bits_per_node; ++j) {
             std::fill(worst.begin(), worst.end(), 0u);
             std::fill(progress.begin(), progress.end(), 0);
             for (auto& c : cells) {
@@ -564,20 +575,27 @@ struct AclBuilder {
         }
         if (!nchosen) return make_leaf(rs);
 
-        uint64_t me = nodes.size() / kAclNodeEntries;
-        nodes.resize(nodes.size() + kAclNodeEntries, make_leaf({}));
+        const size_t base = nodes.size();
+        nodes.resize(base + ((size_t)1 << nchosen), make_leaf({}));
         if (bytes() > budget_bytes) over_budget = true;
-        uint64_t entry = me;
-        for (int q = 0; q < kBitsPerNode; ++q)
-            entry |= (uint64_t)(q < nchosen ? (uint32_t)chosen[q] : kAclNoBit) << (28 + 9 * q);
+        // fields: unused ones (reading the zero row) first, then the chosen bits, first chosen = most significant
+        uint16_t field[kAclMaxNodeBits];
+        for (int q = 0; q < kAclMaxNodeBits; ++q) {
+            int c = q - (kAclMaxNodeBits - nchosen);
+            field[q] = c < 0 ? (uint16_t)kAclZeroField : (uint16_t)((chosen[c] >> 5) * 128 + (31 - (chosen[c] & 31)));
+        }
+        AclEntry entry;
+        entry.x = (uint32_t)base;
+        entry.y = field[0] | (uint32_t)field[1] << 16;
+        entry.z = field[2] | (uint32_t)field[3] << 16;
+        entry.w = field[4] | (uint32_t)field[5] << 16;
         node_memo[memo_key] = entry;
         uint32_t f[kAclKeyWords];
         memcpy(f, fixed, sizeof(f));
         for (int q = 0; q < nchosen; ++q) f[chosen[q] >> 5] |= 1u << (31 - (chosen[q] & 31));
-        // the first chosen bit is the most significant bit of the child index; unused positions add nothing
         for (int idx = 0; idx < (1 << nchosen); ++idx) {
-            uint64_t child = build(cells[idx], f, depth + 1);
-            nodes[(size_t)me * kAclNodeEntries + idx] = child;
+            AclEntry child = build(cells[idx], f, depth + 1);
+            nodes[base + idx] = child;
         }
         return entry;
     }
@@ -595,7 +613,7 @@ void build_acl(Blob& blob, const std::vector<AclRec>& recs, ImageHeader& H) {
     H.acl_ntrees = 0;
     if (!n) {
         H.acl_nodes_off = H.acl_leaf_off = H.acl_rule_off = H.acl_res_off = blob.reserve(32, 0);
-        H.acl_nnodes = H.acl_nleafwords = 0;
+        H.acl_nentries = H.acl_nleafwords = 0;
         return;
     }
     std::vector<AclBuilder::R> rules(n);
@@ -607,16 +625,19 @@ void build_acl(Blob& blob, const std::vector<AclRec>& recs, ImageHeader& H) {
     };
     // Try the cheapest lookups first: one tree over all rules, then forests split by which of
     // (dst, dport, src) a rule leaves open; take the first that fits the memory budget.
-    const int feature_sets[4] = {0, 1, 5, 7};
+    // Wider nodes mean fewer dependent loads; they are tried first and given up for memory.
+    const int feature_sets[6] = {0, 0, 0, 1, 5, 7}, node_bits[6] = {6, 5, 4, 4, 4, 4};
     const char* force = getenv("SFC_ACL_FEAT");
+    const char* force_bits = getenv("SFC_ACL_BITS");
     const char* budget_env = getenv("SFC_ACL_BUDGET_MB");
-    const size_t budget = (budget_env ? (size_t)atoi(budget_env) : 24) << 20;
+    const size_t budget = (budget_env ? (size_t)atoi(budget_env) : 40) << 20;
     AclBuilder B;
-    for (int attempt = 0; attempt < 4; ++attempt) {
+    for (int attempt = 0; attempt < 6; ++attempt) {
         const int feat = force ? atoi(force) : feature_sets[attempt];
         B = AclBuilder();
         B.rules = rules;
-        B.budget_bytes = (force || attempt == 3) ? ~(size_t)0 : budget;
+        B.bits_per_node = force_bits ? std::min(std::max(atoi(force_bits), 1), kAclMaxNodeBits) : (force ? 4 : node_bits[attempt]);
+        B.budget_bytes = (force || attempt == 5) ? ~(size_t)0 : budget;
         std::vector<std::vector<uint16_t>> cat(8);
         for (uint32_t i = 0; i < n; ++i) {
             const uint32_t* m = rules[i].mask;
@@ -639,10 +660,10 @@ void build_acl(Blob& blob, const std::vector<AclRec>& recs, ImageHeader& H) {
         for (auto& g : groups) H.acl_roots[H.acl_ntrees++] = B.build(g, fixed0, 0);
         if (!B.over_budget || force) break;
     }
-    H.acl_nnodes = (uint32_t)(B.nodes.size() / kAclNodeEntries);
+    H.acl_nentries = (uint32_t)B.nodes.size();
     H.acl_nleafwords = (uint32_t)B.leaves.size();
-    H.acl_nodes_off = blob.reserve(std::max<size_t>(B.nodes.size() * 8, 16), 0);
-    if (!B.nodes.empty()) memcpy(blob.at<uint8_t>(H.acl_nodes_off), B.nodes.data(), B.nodes.size() * 8);
+    H.acl_nodes_off = blob.reserve(std::max<size_t>(B.nodes.size() * sizeof(AclEntry), 16), 0);
+    if (!B.nodes.empty()) memcpy(blob.at<uint8_t>(H.acl_nodes_off), B.nodes.data(), B.nodes.size() * sizeof(AclEntry));
     H.acl_leaf_off = blob.reserve(std::max<size_t>(B.leaves.size() * 2, 16), 0);
     memcpy(blob.at<uint8_t>(H.acl_leaf_off), B.leaves.data(), B.leaves.size() * 2);
     H.acl_rule_off = blob.reserve((size_t)n * kAclRuleWords * 4, 0);
@@ -765,7 +786,7 @@ const char* validate_image(const uint8_t* img, size_t len) {
               H.flow4_nhash <= kMaxHashes && H.flow6_nhash >= 1 && H.flow6_nhash <= kMaxHashes && H.flow4_nbuckets &&
               H.flow6_nbuckets && H.acl_nrules <= SFC_MAX_ACL_RULES && H.acl_ntrees <= kAclMaxTrees;
     if (ok && H.acl_nrules)
-        ok = inside(H.acl_nodes_off, (uint64_t)H.acl_nnodes * kAclNodeEntries * 8) &&
+        ok = inside(H.acl_nodes_off, (uint64_t)H.acl_nentries * sizeof(AclEntry)) &&
              inside(H.acl_leaf_off, (uint64_t)H.acl_nleafwords * 2) &&
              inside(H.acl_rule_off, (uint64_t)H.acl_nrules * kAclRuleWords * 4) &&
              inside(H.acl_res_off, (uint64_t)H.acl_nrules * 4);

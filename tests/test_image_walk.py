@@ -26,13 +26,13 @@ def expand_seed(seed, n):
 
 
 class Image:
-    """Field offsets follow struct ImageHeader (version 8)."""
+    """Field offsets follow struct ImageHeader (version 9)."""
 
     def __init__(self, img: np.ndarray):
         self.b = img.tobytes()
         u = lambda fmt, off: struct.unpack_from("<" + fmt, self.b, off)  # noqa: E731
         magic, ver, hb, total, epoch = u("QIIQQ", 0)
-        assert magic == 0x3130434653303042 and ver == 8 and hb == 512 and total == len(self.b)
+        assert magic == 0x3130434653303042 and ver == 9 and hb == 512 and total == len(self.b)
         o = 32
         self.f4_off, self.f4_seed, self.f4_nb, self.f4_nh, self.f4_cnt, self.f4_first = u("QQIIII", o); o += 32
         self.f6_off, self.f6_seed, self.f6_nb, self.f6_nh, self.f6_cnt, self.f6_first = u("QQIIII", o); o += 32
@@ -40,8 +40,9 @@ class Image:
         self.lpm4 = u("QQQII", o); o += 32
         self.lpm6 = u("QQQII", o); o += 32
         self.acl_nodes_off, self.acl_leaf_off, self.acl_rule_off, self.acl_res_off = u("QQQQ", o); o += 32
-        self.acl_nrules, self.acl_nnodes, self.acl_nleaf, self.acl_ntrees = u("IIII", o); o += 16
-        self.acl_roots = u("8Q", o); o += 64
+        self.acl_nrules, self.acl_nentries, self.acl_nleaf, self.acl_ntrees = u("IIII", o); o += 16
+        roots = u("32I", o); o += 128
+        self.acl_roots = [roots[4 * i: 4 * i + 4] for i in range(8)]
         self.lpm4_tail_off, self.lpm6_tail_off, self.lpm4_ntails, self.lpm6_ntails = u("QQII", o)
 
     def u32(self, off, n):
@@ -49,37 +50,44 @@ class Image:
 
     # ---- ACL forest: returns winning rule word (id | deny<<31) or None ----
     def acl(self, q, stats=None):  # q: 11 key words
-        LEAF, PTR = 1 << 27, (1 << 27) - 1
+        LEAF, MORE, OFF, NONE = 1 << 31, 1 << 30, (1 << 28) - 1, 0xFFFF
         groups = ((1, 2, 7, 3), (0, 8, 9, 10), (4, 5, 6))
+        rows = list(q) + [0]  # row 11 is the zero row unused fields point at
         best = None
+
+        def matches(c):
+            if stats is not None:
+                stats["compares"] += 1
+            rec = self.u32(self.acl_rule_off + (c & 0x0FFF) * 96, 24)
+            ok = all(((q[w] ^ int(rec[j])) & int(rec[4 + j])) == 0 for j, w in enumerate(groups[0]))
+            if ok and c & 0x1000:
+                ok = all(((q[w] ^ int(rec[8 + j])) & int(rec[12 + j])) == 0 for j, w in enumerate(groups[1]))
+            if ok and c & 0x2000:
+                ok = all(((q[w] ^ int(rec[16 + j])) & int(rec[20 + j])) == 0 for j, w in enumerate(groups[2]))
+            return ok
+
         for t in range(self.acl_ntrees):
             e = self.acl_roots[t]
-            while not e & LEAF:
+            while not e[0] & LEAF:
                 idx = 0
-                for j in range(4):
-                    p = (e >> (28 + 9 * j)) & 0x1FF
-                    if p != 0x1FF:
-                        idx = (idx << 1) | ((q[p >> 5] >> (31 - (p & 31))) & 1)
-                e = int(np.frombuffer(self.b, dtype="<u8", count=1, offset=self.acl_nodes_off + ((e & PTR) * 16 + idx) * 8)[0])
+                for f in (e[1] & 0xFFFF, e[1] >> 16, e[2] & 0xFFFF, e[2] >> 16, e[3] & 0xFFFF, e[3] >> 16):
+                    assert f & 0x60 == 0 and (f >> 7) <= 11
+                    idx = (idx << 1) | ((rows[f >> 7] >> (f & 31)) & 1)
+                assert e[0] + idx < self.acl_nentries
+                e = tuple(int(x) for x in self.u32(self.acl_nodes_off + (e[0] + idx) * 16, 4))
                 if stats is not None:
                     stats["visits"] += 1
-            off = self.acl_leaf_off + (e & PTR) * 2
-            cnt = int(np.frombuffer(self.b, dtype="<u2", offset=off, count=1)[0])
-            for le in np.frombuffer(self.b, dtype="<u2", offset=off + 2, count=cnt):
-                le = int(le)
-                r = le & 0x0FFF
-                if best is not None and r >= best:
+            cands = [e[1] & 0xFFFF, e[1] >> 16, e[2] & 0xFFFF, e[2] >> 16, e[3] & 0xFFFF, e[3] >> 16]
+            if e[0] & MORE:
+                assert NONE not in cands
+                off = self.acl_leaf_off + (e[0] & OFF) * 2
+                cnt = int(np.frombuffer(self.b, dtype="<u2", offset=off, count=1)[0])
+                cands += [int(c) for c in np.frombuffer(self.b, dtype="<u2", offset=off + 2, count=cnt)]
+            for c in cands:
+                if c == NONE or (best is not None and (c & 0x0FFF) >= best):
                     break
-                if stats is not None:
-                    stats["compares"] += 1
-                rec = self.u32(self.acl_rule_off + r * 96, 24)
-                ok = all(((q[w] ^ int(rec[j])) & int(rec[4 + j])) == 0 for j, w in enumerate(groups[0]))
-                if ok and le & 0x1000:
-                    ok = all(((q[w] ^ int(rec[8 + j])) & int(rec[12 + j])) == 0 for j, w in enumerate(groups[1]))
-                if ok and le & 0x2000:
-                    ok = all(((q[w] ^ int(rec[16 + j])) & int(rec[20 + j])) == 0 for j, w in enumerate(groups[2]))
-                if ok:
-                    best = r
+                if matches(c):
+                    best = c & 0x0FFF
                     break
         return None if best is None else int(self.u32(self.acl_res_off + best * 4, 1)[0])
 
