@@ -108,10 +108,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 // same wait, for the producer lane: it only needs to wake up once per tile, so let the hardware park
 // it for a while between polls instead of burning issue slots the consumer warps could use
-__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
 #ifndef SFC_PRODUCER_HINT_NS
 #define SFC_PRODUCER_HINT_NS 2000
 #endif
+#ifndef SFC_PRODUCER_HINT_NS_ACL
+#define SFC_PRODUCER_HINT_NS_ACL 16000  // an ACL tile takes several microseconds: poll less often
+#endif
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity, uint32_t hint_ns) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "WAITR_%=:\n\t"
@@ -119,7 +122,7 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
         "@p bra DONER_%=;\n\t"
         "bra WAITR_%=;\n\t"
         "DONER_%=:\n\t}" ::"r"(smem_u32(bar)),
-        "r"(parity), "r"((uint32_t)SFC_PRODUCER_HINT_NS)
+        "r"(parity), "r"(hint_ns)
         : "memory");
 }
 __device__ __forceinline__ void tma_load_tile(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar,
@@ -148,6 +151,9 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
     uint4 v;
     asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
     return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
 // one key bit of the ACL stage: `field` = row offset | right shift (see sfc_common.h), appended to idx
 __device__ __forceinline__ uint32_t acl_key_bit(uint32_t key_base, uint32_t field, uint32_t idx) {
@@ -319,12 +325,13 @@ __device__ __forceinline__ uint32_t lpm_word_mask(uint32_t len, int i) {  // bit
     const int bits = (int)len - 32 * i;
     return bits <= 0 ? 0u : (bits >= 32 ? 0xFFFFFFFFu : ~(0xFFFFFFFFu >> bits));
 }
-template <int MAX_BITS>
+// `a` = the destination as four words; an IPv4 address sits in a[0] with a[1..3] = 0, and its trie never
+// has a child below bit 32, so the same walk serves both families.
 __device__ __forceinline__ uint32_t lpm_lookup(const uint32_t* __restrict__ root, const uint32_t* __restrict__ nodes,
                                                const LpmTail* __restrict__ tails, const uint32_t* a) {
     uint32_t e = __ldg(root + (a[0] >> 16));
 #pragma unroll
-    for (int pos = 16; pos < MAX_BITS; pos += 8) {  // static positions: the address stays in registers
+    for (int pos = 16; pos < 128; pos += 8) {  // static positions: the address stays in registers
         if (!(e & kLpmChild)) break;
         uint32_t byte = (a[pos >> 5] >> (24 - (pos & 31))) & 0xFFu;
         e = __ldg(nodes + (size_t)(e & ~kLpmChild) * 256 + byte);
@@ -333,11 +340,9 @@ __device__ __forceinline__ uint32_t lpm_lookup(const uint32_t* __restrict__ root
     if (e & kLpmTail) {  // a lone prefix below this point: one record, one masked compare
         uint32_t t[8];
         ldg256(tails + (e & ~kLpmTail), t);
-        uint32_t d = (a[0] ^ t[0]) & lpm_word_mask(t[4], 0);
-        if (MAX_BITS > 32) {
+        uint32_t d = 0;
 #pragma unroll
-            for (int i = 1; i < 4; ++i) d |= (a[i] ^ t[i]) & lpm_word_mask(t[4], i);
-        }
+        for (int i = 0; i < 4; ++i) d |= (a[i] ^ t[i]) & lpm_word_mask(t[4], i);
         e = d ? t[6] : t[5];
     }
     return e;
@@ -407,7 +412,7 @@ __global__ void __launch_bounds__(TILE + 32, ACL ? SFC_MINB_ACL : SFC_MINB) clas
                 const bool have = tile < n_tiles;
                 uint32_t next = 0;
                 if (have) next = gridDim.x + atomicAdd(ticket, 1u);
-                if (use > 0) mbar_wait_relaxed(empty + s, (use - 1) & 1);
+                if (use > 0) mbar_wait_relaxed(empty + s, (use - 1) & 1, ACL ? SFC_PRODUCER_HINT_NS_ACL : SFC_PRODUCER_HINT_NS);
                 tile_of[s] = have ? tile : 0xFFFFFFFFu;
                 if (!have) {
                     mbar_arrive(full + s);  // end marker: no bytes will follow
@@ -519,19 +524,18 @@ __global__ void __launch_bounds__(TILE + 32, ACL ? SFC_MINB_ACL : SFC_MINB) clas
         // matches all 11 key words under its mask wins, and the best rank over the trees is the
         // verdict.  The key words sit in shared memory because the tested bit positions are table data.
         if (ACL) {
-            uint32_t* q = aclq + (tid >> 5) * (kAclKeyRows * 32) + lane;
+            const uint32_t qb = smem_u32(aclq + (tid >> 5) * (kAclKeyRows * 32) + lane);
             const uint32_t q0 = (port << 16) | (k.meta >> 8);
             const uint32_t q1 = (k.ip_ver << 24) | ((k.meta & 0xFFu) << 16) | (k.ports >> 16), q2 = k.ports << 16;
-            q[0 * 32] = q0;
-            q[1 * 32] = q1;
-            q[2 * 32] = q2;
+            sts32(qb + 0 * 128, q0);
+            sts32(qb + 1 * 128, q1);
+            sts32(qb + 2 * 128, q2);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                q[(3 + i) * 32] = k.sip[i];
-                q[(7 + i) * 32] = k.dip[i];
+                sts32(qb + (3 + i) * 128, k.sip[i]);
+                sts32(qb + (7 + i) * 128, k.dip[i]);
             }
             if (live && is_ip) {
-                const uint32_t qb = smem_u32(q);
                 uint32_t best = 0xFFFFFFFFu;
                 // full compare of candidate c against the key held in registers; g = its G0 sector
                 auto matches = [&](uint32_t c, const uint32_t* g) -> bool {
@@ -662,18 +666,15 @@ __global__ void __launch_bounds__(TILE + 32, ACL ? SFC_MINB_ACL : SFC_MINB) clas
         }
 
         // ---- stage 4: LPM on the destination ----
+        // One code path for both families: a warp holding IPv4 and IPv6 packets walks the two tries side
+        // by side (max of the depths) instead of one after the other (their sum).
         if (!done && is_ip) {
-            if (k.ip_ver == 4 && T.lpm4_count) {
-                uint32_t e = lpm_lookup<32>(T.lpm4_root, T.lpm4_nodes, T.lpm4_tails, k.dip);
+            const bool v6 = k.ip_ver == 6;
+            if (v6 ? T.lpm6_count : T.lpm4_count) {
+                const uint32_t e = lpm_lookup(v6 ? T.lpm6_root : T.lpm4_root, v6 ? T.lpm6_nodes : T.lpm4_nodes,
+                                              v6 ? T.lpm6_tails : T.lpm4_tails, k.dip);
                 if (e) {
-                    uint2 r = __ldg(reinterpret_cast<const uint2*>(T.lpm4_nh + (e - 1)));
-                    rhi = r.x;
-                    rlo = r.y;
-                }
-            } else if (k.ip_ver == 6 && T.lpm6_count) {
-                uint32_t e = lpm_lookup<128>(T.lpm6_root, T.lpm6_nodes, T.lpm6_tails, k.dip);
-                if (e) {
-                    uint2 r = __ldg(reinterpret_cast<const uint2*>(T.lpm6_nh + (e - 1)));
+                    uint2 r = __ldg(reinterpret_cast<const uint2*>((v6 ? T.lpm6_nh : T.lpm4_nh) + (e - 1)));
                     rhi = r.x;
                     rlo = r.y;
                 }
