@@ -6,6 +6,7 @@
 #include <errno.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -36,7 +37,7 @@ constexpr int kTileAcl = SFC_TILE_ACL;
 constexpr int kStagesAcl = SFC_STAGES_ACL;
 template <bool A>
 constexpr int stages_for() { return A ? kStagesAcl : kStages; }
-constexpr int kTicketRing = 32;      // a launch uses slot seq % 32; slots are 32 bytes apart and self-resetting
+constexpr int kTicketRing = 256;     // a launch uses slot seq % 256 (so up to 256 launches may be in flight); slots are 32 bytes apart and self-resetting
 constexpr int kTicketStride = 8;     // u32 words per slot: {draw counter, finished producers, pad}
 constexpr size_t kHostChunk = 1u << 18;  // packets per pipelined chunk in sfc_classify_host
 
@@ -56,15 +57,13 @@ struct sfc_handle {
     uint64_t epoch = 0;
     DevTables T{};
     unsigned long long* d_counters = nullptr;
-    uint64_t launches = 0;
+    std::atomic<uint64_t> launches{0};  // data-plane threads on different streams share the handle
     EncodeTiledFn encode = nullptr;
     int ctas_per_sm[20] = {0};  // 0-3 shipped variants, 4-12 tune variants, 16-19 multi-batch variants
     int tune_tile = 0, tune_stages = 0;  // SFC_TUNE=tile,stages (experiments)
     int tune_ctas = 0, tune_carveout = -1;  // cap on resident CTAs per SM / shared-memory carveout percent
     uint32_t flow_first[2] = {0, 0};
     int probe_mode = -1;  // option "flow_probe_mode": -1 auto, else kProbe* bits
-    BatchList batch_list{};               // sfc_classify_batches: the list being laid out for the next launch
-    uintptr_t batch_hdr[kMaxBatches]{};   //   and the header address of each of its entries
     uint32_t* d_tickets = nullptr;  // ring of kTicketRing tile-ticket counters (scratch of the classify kernel)
     // sfc_classify_host staging
     cudaStream_t hs[2] = {nullptr, nullptr};
@@ -109,9 +108,16 @@ struct DeviceGuard {
     int prev = -1;
     explicit DeviceGuard(int dev) {
         if (dev < 0) return;
+        // A thread that has made no runtime call yet reports device 0 as current but has no driver context
+        // bound, and cuTensorMapEncodeTiled (a driver entry point) then fails with INVALID_CONTEXT: the
+        // first call of every thread binds the primary context explicitly.
+        static thread_local int bound = -1;
         cudaGetDevice(&prev);
-        if (prev != dev) cudaSetDevice(dev);
-        else prev = -1;
+        if (prev != dev || bound != dev) {
+            cudaSetDevice(dev);
+            bound = dev;
+        }
+        if (prev == dev) prev = -1;
     }
     ~DeviceGuard() {
         if (prev >= 0) cudaSetDevice(prev);
@@ -224,7 +230,7 @@ int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_
     int per_sm = h->ctas_per_sm[slot];
     if ((flags & SFC_F_OVERLAP) && h->tune_ctas == 0) per_sm = 1;
     uint64_t grid = std::min<uint64_t>(n_tiles, (uint64_t)h->sm_count * per_sm);
-    uint32_t* ticket = h->d_tickets + (h->launches % kTicketRing) * kTicketStride;
+    uint32_t* ticket = h->d_tickets + (h->launches.fetch_add(1) % kTicketRing) * kTicketStride;
     uint32_t overlap = (flags & SFC_F_OVERLAP) ? 1u : 0u;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
@@ -238,7 +244,6 @@ int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_
     cfg.numAttrs = overlap ? 1 : 0;
     CUDA_TRY(h, cudaLaunchKernelEx(&cfg, kern, map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, overlap,
                                    h->T, NoBatches{}));
-    ++h->launches;
     return 0;
 }
 
@@ -267,7 +272,7 @@ int launch_multi(sfc_handle* h, int slot, const BatchList& L, uint64_t rows, uin
     if (r != CUDA_SUCCESS) return fail(h, -EIO, "cuTensorMapEncodeTiled failed (%d)", (int)r);
     int per_sm = (flags & SFC_F_OVERLAP) ? 1 : h->ctas_per_sm[slot];
     uint64_t grid = std::min<uint64_t>(n_tiles, (uint64_t)h->sm_count * per_sm);
-    uint32_t* ticket = h->d_tickets + (h->launches % kTicketRing) * kTicketStride;
+    uint32_t* ticket = h->d_tickets + (h->launches.fetch_add(1) % kTicketRing) * kTicketStride;
     uint32_t overlap = (flags & SFC_F_OVERLAP) ? 1u : 0u;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
@@ -281,7 +286,6 @@ int launch_multi(sfc_handle* h, int slot, const BatchList& L, uint64_t rows, uin
     cfg.numAttrs = overlap ? 1 : 0;
     CUDA_TRY(h, cudaLaunchKernelEx(&cfg, kern, map, (const uint16_t*)nullptr, (uint64_t*)nullptr, 0u, n_tiles, ticket,
                                    overlap, h->T, L));
-    ++h->launches;
     return 0;
 }
 
@@ -845,7 +849,7 @@ long sfc_stat(const sfc_handle* h, const char* name) {
     if (!strcmp(name, "patched_buckets")) return (long)h->n_patched_buckets;
     if (!strcmp(name, "flows")) return (long)h->rs.flows.size();
     if (!strcmp(name, "flow4_first_bucket")) return (long)h->flow_first[0];
-    if (!strcmp(name, "launches")) return (long)h->launches;
+    if (!strcmp(name, "launches")) return (long)h->launches.load();
     return -ENOENT;
 }
 
@@ -957,7 +961,8 @@ int sfc_classify_batches(sfc_handle* h, const sfc_batch* batches, uint32_t n_bat
     // Greedy split into launches: at most kMaxBatches descriptors, 2^31 tiles and 2^31 rows of span each
     // (TMA coordinates are signed 32-bit).
     constexpr uint64_t kMaxRows = (1ull << 31) - 2 * kTile;
-    BatchList& L = h->batch_list;
+    BatchList L;                       // on the stack: callers on different streams do not share it
+    uintptr_t batch_hdr[kMaxBatches];  // header address of each entry until the lowest one is known
     uint32_t i = 0;
     while (i < n_batches) {
         L.count = 0;
@@ -979,12 +984,12 @@ int sfc_classify_batches(sfc_handle* h, const sfc_batch* batches, uint32_t n_bat
             d.pad = 0;
             d.in_port = b.in_port;
             d.result = b.result;
-            h->batch_hdr[L.count - 1] = p;
+            batch_hdr[L.count - 1] = p;
             tiles += t;
         }
         if (!L.count) break;  // only empty batches were left
         L.base = (const uint8_t*)lo;
-        for (uint32_t k = 0; k < L.count; ++k) L.b[k].row0 = (uint32_t)((h->batch_hdr[k] - lo) / 64);
+        for (uint32_t k = 0; k < L.count; ++k) L.b[k].row0 = (uint32_t)((batch_hdr[k] - lo) / 64);
         const uint64_t rows = (hi - lo) / 64;
         int rc;
         if (c && a) rc = launch_multi<true, true>(h, 19, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
@@ -1072,7 +1077,7 @@ int sfc_counters_reset(sfc_handle* h) {
 }
 
 void* sfc_counters_device_ptr(sfc_handle* h) { return h ? (void*)h->d_counters : nullptr; }
-uint64_t sfc_launch_count(const sfc_handle* h) { return h ? h->launches : 0; }
+uint64_t sfc_launch_count(const sfc_handle* h) { return h ? h->launches.load() : 0; }
 float sfc_last_kernel_ms(const sfc_handle* h) { return h ? h->last_kernel_ms : -1.f; }
 
 // =================================================================== no-allocation call ==

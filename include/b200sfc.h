@@ -277,7 +277,8 @@ int sfc_table_import_device(sfc_handle* h, const void* dptr, size_t len, void* c
 
 /* Classify n packets.  hdr (n x 64 B, 16-byte aligned), in_port (n x u16) and result (n x u64)
  * are DEVICE pointers on the handle's device.  Asynchronous on `cuda_stream` (a cudaStream_t,
- * NULL = legacy default stream).  One caller thread per stream.
+ * NULL = legacy default stream).  One caller thread per stream; threads on different streams may
+ * share the handle (up to 256 classify launches in flight per handle).
  * No reference counterpart — this is the lookup the reference delegates to OVS / FXP hardware. */
 int sfc_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result,
                  size_t n, uint32_t flags, void* cuda_stream);

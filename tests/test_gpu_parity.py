@@ -395,3 +395,39 @@ def test_acl_3000_rules_single_tree_and_forests(torch_cuda, feat, monkeypatch):
     assert_same(got, want, hdr)
     assert np.array_equal(dp.counters_read(), cnt)
     assert (sfc.result_fields(got)[3] == consts.STAGE_ACL).sum() > 100
+
+
+def test_two_threads_two_streams_share_one_handle(torch_cuda):
+    """Data-plane threads, one stream each, may share a handle (header: one caller thread per stream)."""
+    import threading
+    t = torch_cuda
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    spec = config2_spec()
+    install_flows(sc, spec)
+    dp.commit()
+    n, rounds = 1 << 16, 200
+    hdr, ports = gen_dev(t, dp, spec, 0, 2 * n)
+    want = sc.orc.classify(hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), threads=8)
+    res = t.zeros((2, rounds, n), dtype=t.int64, device="cuda")
+    streams = [t.cuda.Stream(), t.cuda.Stream()]
+    errors = []
+
+    def worker(i):
+        try:
+            for r in range(rounds):
+                dp.classify(hdr.data_ptr() + i * n * 64, ports.data_ptr() + i * n * 2, res[i, r].data_ptr(), n,
+                            consts.F_OVERLAP if r % 2 else 0, streams[i].cuda_stream)
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(2)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    t.cuda.synchronize()
+    assert not errors, errors
+    for i in range(2):
+        w = t.from_numpy(want[i * n:(i + 1) * n].view(np.int64).copy()).cuda()
+        assert bool((res[i] == w).all()), f"thread {i}: some launch produced different results"
