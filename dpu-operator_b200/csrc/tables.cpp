@@ -790,7 +790,65 @@ const char* validate_image(const uint8_t* img, size_t len) {
              inside(H.acl_leaf_off, (uint64_t)H.acl_nleafwords * 2) &&
              inside(H.acl_rule_off, (uint64_t)H.acl_nrules * kAclRuleWords * 4) &&
              inside(H.acl_res_off, (uint64_t)H.acl_nrules * 4);
-    return ok ? nullptr : "image: a section lies outside the buffer or a field is out of range";
+    if (!ok) return "image: a section lies outside the buffer or a field is out of range";
+
+    // Everything the kernel follows as an index is checked here once, so that a damaged or hostile image
+    // is refused on the host instead of faulting on the device.  Flow and L2 tables hold no indices.
+    auto lpm_ok = [&](uint64_t root_off, uint64_t nodes_off, uint32_t nnodes, uint64_t tail_off, uint32_t ntails,
+                      uint64_t nh_off) {
+        auto value_ok = [&](uint32_t v) { return v == 0 || inside(nh_off + (uint64_t)(v - 1) * sizeof(LpmRes), sizeof(LpmRes)); };
+        auto entry_ok = [&](uint32_t e) {
+            if (e & kLpmChild) return (e & ~kLpmChild) < nnodes;
+            if (e & kLpmTail) return (e & ~kLpmTail) < ntails;
+            return value_ok(e);
+        };
+        const uint32_t* root = (const uint32_t*)(img + root_off);
+        for (uint32_t i = 0; i < 65536; ++i)
+            if (!entry_ok(root[i])) return false;
+        const uint32_t* nodes = (const uint32_t*)(img + nodes_off);
+        for (uint64_t i = 0; i < (uint64_t)nnodes * 256; ++i)
+            if (!entry_ok(nodes[i])) return false;
+        const LpmTail* tails = (const LpmTail*)(img + tail_off);
+        for (uint32_t i = 0; i < ntails; ++i)
+            if (tails[i].len > 128 || (tails[i].match & (kLpmChild | kLpmTail)) || (tails[i].fallback & (kLpmChild | kLpmTail)) ||
+                !value_ok(tails[i].match) || !value_ok(tails[i].fallback))
+                return false;
+        return true;
+    };
+    if (!lpm_ok(H.lpm4_root_off, H.lpm4_nodes_off, H.lpm4_nnodes, H.lpm4_tail_off, H.lpm4_ntails, H.lpm4_nh_off) ||
+        !lpm_ok(H.lpm6_root_off, H.lpm6_nodes_off, H.lpm6_nnodes, H.lpm6_tail_off, H.lpm6_ntails, H.lpm6_nh_off))
+        return "image: an LPM entry points outside its table";
+    if (H.acl_nrules) {
+        const uint16_t* leaves = (const uint16_t*)(img + H.acl_leaf_off);
+        auto cand_ok = [&](uint32_t c) { return c == kAclNone || (c & kAclRankMask) < H.acl_nrules; };
+        auto field_ok = [&](uint32_t f) { return (f & 0x60u) == 0 && (f >> 7) < (uint32_t)kAclKeyRows; };
+        auto entry_ok = [&](const AclEntry& e) {
+            const uint32_t h[6] = {e.y & 0xFFFFu, e.y >> 16, e.z & 0xFFFFu, e.z >> 16, e.w & 0xFFFFu, e.w >> 16};
+            if (e.x & kAclLeafBit) {
+                for (uint32_t c : h)
+                    if (!cand_ok(c)) return false;
+                if (e.x & kAclMoreBit) {
+                    const uint64_t off = e.x & kAclOffMask;
+                    if (off >= H.acl_nleafwords || off + 1 + leaves[off] > H.acl_nleafwords) return false;
+                    for (uint32_t i = 1; i <= leaves[off]; ++i)
+                        if (!cand_ok(leaves[off + i]) || leaves[off + i] == kAclNone) return false;
+                }
+                return true;
+            }
+            uint64_t max_idx = 0;  // fields naming the zero row contribute a 0 bit wherever they stand
+            for (uint32_t f : h) {
+                if (!field_ok(f)) return false;
+                max_idx = (max_idx << 1) | ((f >> 7) != 11u ? 1u : 0u);
+            }
+            return (uint64_t)e.x + max_idx < H.acl_nentries;
+        };
+        const AclEntry* nodes = (const AclEntry*)(img + H.acl_nodes_off);
+        for (uint32_t t = 0; t < H.acl_ntrees; ++t)
+            if (!entry_ok(H.acl_roots[t])) return "image: an ACL root entry is out of range";
+        for (uint32_t i = 0; i < H.acl_nentries; ++i)
+            if (!entry_ok(nodes[i])) return "image: an ACL tree entry is out of range";
+    }
+    return nullptr;
 }
 
 }  // namespace sfc

@@ -5,6 +5,7 @@ oracle's.  The walker lives in the tests on purpose: the library has no CPU look
 import struct
 
 import numpy as np
+import pytest
 
 from common import Oracle, Scenario, config3_spec, config4_spec, consts, install_flows, install_lpm_acl, sfc
 
@@ -227,3 +228,45 @@ def test_forced_forests_answer_like_the_single_tree(monkeypatch):
         answers.append((img.acl_ntrees, out))
     assert answers[0][0] == 1 and answers[3][0] > answers[1][0] >= 2
     assert all(a[1] == answers[0][1] for a in answers[1:])
+
+
+def test_import_refuses_images_whose_indices_point_outside_their_tables():
+    """sfc_table_import follows every index the kernel would follow (LPM children, tails and next hops,
+    ACL child arrays, candidates and overflow lists) and refuses the image instead of letting the device fault."""
+    import errno
+    import struct as st
+    sc = Scenario(sfc.Dataplane(-1))
+    spec = config4_spec(n_pfx4=3000, n_pfx6=800, n_acl=400)
+    install_lpm_acl(sc, spec)
+    sc.dp.commit()
+    good = sc.dp.table_export()
+    img = Image(good)
+    other = sfc.Dataplane(-1)
+    other.table_import(good)  # the untouched image is accepted
+    assert np.array_equal(other.table_export(), good)
+
+    def refused(mutate):
+        bad = good.copy()
+        mutate(bad)
+        with pytest.raises(sfc.SfcError) as e:
+            sfc.Dataplane(-1).table_import(bad)
+        assert e.value.code == -errno.EINVAL
+        return str(e.value)
+
+    def put32(buf, off, v):
+        buf[off:off + 4] = np.frombuffer(st.pack("<I", v), dtype=np.uint8)
+
+    root4 = img.lpm4[0]
+    assert "LPM" in refused(lambda b: put32(b, root4 + 4 * 77, 0x80000000 | img.lpm4[3]))       # child past the last node
+    assert "LPM" in refused(lambda b: put32(b, root4 + 4 * 77, 0x40000000 | img.lpm4_ntails))   # tail past the last record
+    assert "LPM" in refused(lambda b: put32(b, root4 + 4 * 77, 0x3FFFFFFF))                     # next hop far outside
+    assert img.lpm6_ntails > 0
+    assert "LPM" in refused(lambda b: put32(b, img.lpm6_tail_off + 16, 129))                    # tail length > 128
+    assert "ACL" in refused(lambda b: put32(b, img.acl_nodes_off, img.acl_nentries))            # child array past the end
+    leaf = next(i for i in range(img.acl_nentries) if int(img.u32(img.acl_nodes_off + 16 * i, 1)[0]) >> 31)
+    assert "ACL" in refused(lambda b: put32(b, img.acl_nodes_off + 16 * leaf + 4, 0x0FFF))      # candidate rank >= nrules
+    assert "ACL" in refused(lambda b: put32(b, img.acl_nodes_off + 16 * leaf, 0xC0000000 | img.acl_nleaf))  # overflow list outside
+    assert "ACL" in refused(lambda b: put32(b, 32 * 6 + 32 + 16, img.acl_nentries))             # root entry (header)
+    assert refused(lambda b: put32(b, 8, 8))                                                     # older image version
+    with pytest.raises(sfc.SfcError):
+        sfc.Dataplane(-1).table_import(good[:-256])                                               # truncated
