@@ -79,3 +79,39 @@ def test_port_registry_semantics():
     assert dp.port_list() == ["vf0-1"]
     assert dp.port_add("nf-in") == 0  # lowest free id is reused
     assert dp.port_lookup("vf0-1") == 1
+
+
+def test_header_is_plain_c_and_a_c_program_links_against_the_library(tmp_path):
+    """The boundary is a C ABI: a C11 translation unit (what cgo compiles) must take both headers as they
+    are, link against the library and drive the control plane of an offline handle."""
+    import shutil
+    import subprocess
+    if not shutil.which("gcc"):
+        pytest.skip("no gcc")
+    src = tmp_path / "abi.c"
+    src.write_text(r'''
+#include <stdio.h>
+#include <string.h>
+#include "b200sfc.h"
+#include "b200vsp.h"
+int main(void) {
+    sfc_handle* h = NULL;
+    if (sfc_create(-1, &h) != 0) return 1;
+    uint16_t a = 0, b = 0;
+    if (sfc_port_add(h, "vf0", &a) || sfc_port_add(h, "nf0-in", &b)) return 2;
+    if (sfc_l2_rule_add(h, a, b, NULL, NULL)) return 3;
+    sfc_batch batch; memset(&batch, 0, sizeof batch);
+    if (sizeof(sfc_batch) != 32 || sizeof(sfc_flow_key) != 40 || sizeof(sfc_acl_rule) != 88) return 4;
+    if (sfc_commit(h)) return 5;
+    if (sfc_classify(h, &batch, &a, (uint64_t*)&batch, 1, 0, NULL) == 0) return 6;  /* offline: must refuse */
+    printf("%s|%zu|%s\n", sfc_version(), sfc_table_size(h), sfc_last_error(h));
+    return sfc_destroy(h);
+}
+''')
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    libdir = os.path.join(root, "dpu-operator_b200")
+    exe = tmp_path / "abi"
+    subprocess.run(["gcc", "-std=c11", "-Wall", "-Werror", "-pedantic", "-I", os.path.join(root, "include"), str(src), "-o", str(exe),
+                    "-L", libdir, "-lb200sfc", f"-Wl,-rpath,{libdir}"], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.strip().split("|")
+    assert out[0].startswith("b200sfc") and int(out[1]) > 512 and "offline" in out[2]
