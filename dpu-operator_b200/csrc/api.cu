@@ -138,12 +138,14 @@ void fill_tables(DevTables& T, const ImageHeader& H, const uint8_t* b, unsigned 
         // stays in L2 next to the packet stream (measured up to 42 MB: 14.3 vs 15.5 us) still gains from
         // issuing both probes at once, without L1; beyond that every probe is a DRAM sector and the
         // second load only adds traffic (eager is 8-40% slower).
-        uint64_t bytes = (uint64_t)H.flow4_nbuckets * kFlow4BucketBytes;
-        uint32_t mode = bytes <= (128u << 10) ? (kProbeEager | kProbeL1) : bytes <= (48u << 20) ? kProbeEager : 0u;
+        uint64_t bytes = (uint64_t)H.flow4_nbuckets * H.flow4_slots * kFlow4BucketBytes;
+        uint32_t mode = bytes <= (128u << 10) ? (kProbeEager | kProbeL1) : bytes <= kFlowL2ResidentBytes ? kProbeEager : 0u;
         if (probe_mode >= 0) mode = (uint32_t)probe_mode;
         T.flow4_mode = mode;
     }
+    T.flow4_slots = H.flow4_slots;
     T.flow6_nbuckets = H.flow6_nbuckets;
+    T.flow6_slots = H.flow6_slots;
     T.flow6_nhash = H.flow6_nhash;
     T.flow6_count = H.flow6_count;
     T.l2x = (const L2Entry*)(b + H.l2x_off);
@@ -426,6 +428,12 @@ int sfc_set_option(sfc_handle* h, const char* name, long value) {
         h->rs.flow_hashes = (int)value;
         return 0;
     }
+    if (!strcmp(name, "flow_slots")) {  // slots per flow bucket: 0 / 1 = one (default), 2 = dense two-slot buckets
+        if (value < 0 || value > 2) return fail(h, -EINVAL, "flow_slots must be 0, 1 or 2");
+        h->rs.other_dirty = true;
+        h->rs.flow_slots = (int)value;
+        return 0;
+    }
     if (!strcmp(name, "flow_probe_mode")) {  // -1 auto, bit0 eager dual probe, bit1 probes may live in L1
         if (value < -1 || value > 3) return fail(h, -EINVAL, "flow_probe_mode must be -1..3");
         h->probe_mode = (int)value;
@@ -704,17 +712,18 @@ namespace {
 void adopt_shadows(sfc_handle* h, const std::vector<uint8_t>& img) {
     memcpy(&h->header, img.data(), sizeof(ImageHeader));
     const ImageHeader& H = h->header;
-    auto take = [&](FlowTable& t, std::vector<uint32_t>& mem, bool v6, uint64_t off, uint32_t nb, uint32_t nhash, uint64_t seed) {
+    auto take = [&](FlowTable& t, std::vector<uint32_t>& mem, bool v6, uint64_t off, uint32_t nb, uint32_t slots, uint32_t nhash, uint64_t seed) {
         t = FlowTable();
         t.v6 = v6;
-        mem.assign((const uint32_t*)(img.data() + off), (const uint32_t*)(img.data() + off) + (size_t)nb * t.words());
+        mem.assign((const uint32_t*)(img.data() + off), (const uint32_t*)(img.data() + off) + (size_t)nb * slots * t.words());
         t.tab = mem.data();
         t.nbuckets = nb;
+        t.slots = (int)slots;
         t.nhash = (int)nhash;
         expand_seed(seed, t.S, v6 ? kFlow6SeedWords : kFlow4SeedWords);
     };
-    take(h->shadow4, h->shadow4_mem, false, H.flow4_off, H.flow4_nbuckets, H.flow4_nhash, H.flow4_seed);
-    take(h->shadow6, h->shadow6_mem, true, H.flow6_off, H.flow6_nbuckets, H.flow6_nhash, H.flow6_seed);
+    take(h->shadow4, h->shadow4_mem, false, H.flow4_off, H.flow4_nbuckets, H.flow4_slots, H.flow4_nhash, H.flow4_seed);
+    take(h->shadow6, h->shadow6_mem, true, H.flow6_off, H.flow6_nbuckets, H.flow6_slots, H.flow6_nhash, H.flow6_seed);
     h->shadow_valid = true;
 }
 
@@ -740,10 +749,13 @@ int full_commit(sfc_handle* h) {
 int incremental_commit(sfc_handle* h, cudaStream_t st, bool async) {
     RuleStore& rs = h->rs;
     if (rs.other_dirty || !h->shadow_valid || (!h->offline() && !h->d_image)) return 0;
-    const int max_load = rs.flow_hashes == 2 ? 45 : 85;
+    auto room = [&](const FlowTable& t) {  // flows the table may hold before it has to be rebuilt larger
+        const long max_load = t.slots == 2 ? 85 : (rs.flow_hashes == 2 ? 45 : 85);
+        return (long)t.nbuckets * t.slots * max_load / 100;
+    };
     long c4 = h->header.flow4_count, c6 = h->header.flow6_count;
     for (auto& ch : rs.flow_log) (ch.rec.ip_ver == 6 ? c6 : c4) += ch.add ? 1 : -1;
-    if (c4 * 100 > (long)h->shadow4.nbuckets * max_load || c6 * 100 > (long)h->shadow6.nbuckets * max_load) return 0;
+    if (c4 > room(h->shadow4) || c6 > room(h->shadow6)) return 0;
     std::vector<uint32_t> dirty4, dirty6;
     // A failed insertion walk leaves the shadow with one flow homeless: fall back to a rebuild, which
     // re-adopts the shadows from the rule store (the source of truth).  Nothing has reached the device yet.

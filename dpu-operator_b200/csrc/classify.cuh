@@ -23,6 +23,7 @@ struct DevTables {
     const uint32_t* flow6;
     uint32_t flow4_nbuckets, flow4_nhash, flow4_count;
     uint32_t flow4_mode;  // kProbeEager: issue both probes at once; kProbeL1: let probes allocate in L1
+    uint32_t flow4_slots, flow6_slots;  // slots per bucket (1 or 2)
     uint32_t flow6_nbuckets, flow6_nhash, flow6_count;
     uint32_t S4[kFlow4SeedWords];
     uint32_t S6[kFlow6SeedWords];
@@ -262,11 +263,33 @@ __device__ __forceinline__ bool flow4_lookup(const DevTables& T, const Key& k, u
     const uint32_t meta20 = k.meta & 0xFFFFFu, tag = meta20 | kSlotValid;
     uint32_t x, y;
     flow4_hash(k.sip[0], k.dip[0], k.ports, meta20, T.S4, x, y);
-    const uint32_t* p0 = T.flow4 + (size_t)flow_bucket(x, y, 0, T.S4 + 4, T.flow4_nbuckets) * kFlow4BucketWords;
-    const uint32_t* p1 = T.flow4 + (size_t)flow_bucket(x, y, 1, T.S4 + 4, T.flow4_nbuckets) * kFlow4BucketWords;
+    const uint32_t bw = kFlow4BucketWords * T.flow4_slots;
+    const uint32_t* p0 = T.flow4 + (size_t)flow_bucket(x, y, 0, T.S4 + 4, T.flow4_nbuckets) * bw;
+    const uint32_t* p1 = T.flow4 + (size_t)flow_bucket(x, y, 1, T.S4 + 4, T.flow4_nbuckets) * bw;
     uint32_t s[8], t[8];
     bool hit;
-    if (T.flow4_mode & kProbeEager) {
+    if (T.flow4_slots == 2) {
+        // dense L2-resident table: the two slots of a bucket are the two halves of one 64-byte line;
+        // both are fetched at once, the second bucket only if neither holds the flow
+        ldg256(p0, s);
+        ldg256(p0 + 8, t);
+        hit = flow4_match(s, k, tag);
+        if (!hit && flow4_match(t, k, tag)) {
+            hit = true;
+            s[4] = t[4];
+            s[5] = t[5];
+        }
+        if (!hit) {
+            ldg256(p1, s);
+            ldg256(p1 + 8, t);
+            hit = flow4_match(s, k, tag);
+            if (!hit && flow4_match(t, k, tag)) {
+                hit = true;
+                s[4] = t[4];
+                s[5] = t[5];
+            }
+        }
+    } else if (T.flow4_mode & kProbeEager) {
         if (T.flow4_mode & kProbeL1) {
             ldg256_l1(p0, s);
             ldg256_l1(p1, t);
@@ -289,9 +312,11 @@ __device__ __forceinline__ bool flow4_lookup(const DevTables& T, const Key& k, u
         }
     }
     if (!hit && T.flow4_nhash > 2) {
-        const uint32_t b2 = flow_bucket(x, y, 2, T.S4 + 4, T.flow4_nbuckets);
-        ldg256(T.flow4 + (size_t)b2 * kFlow4BucketWords, s);
-        hit = flow4_match(s, k, tag);
+        const uint32_t* p2 = T.flow4 + (size_t)flow_bucket(x, y, 2, T.S4 + 4, T.flow4_nbuckets) * bw;
+        for (uint32_t sl = 0; sl < T.flow4_slots && !hit; ++sl) {
+            ldg256(p2 + sl * kFlow4BucketWords, s);
+            hit = flow4_match(s, k, tag);
+        }
     }
     rhi = s[4];
     rlo = s[5];
@@ -314,8 +339,9 @@ __device__ __forceinline__ bool flow6_lookup(const DevTables& T, const Key& k, u
     flow6_hash(k.sip, k.dip, k.ports, meta20, T.S6, x, y);
     bool hit = false;
     for (uint32_t j = 0; j < T.flow6_nhash && !hit; ++j) {
-        uint32_t b = flow_bucket(x, y, (int)j, T.S6 + 10, T.flow6_nbuckets);
-        hit = flow6_probe(T.flow6 + (size_t)b * kFlow6BucketWords, k, tag, rhi, rlo);
+        const uint32_t* p = T.flow6 + (size_t)flow_bucket(x, y, (int)j, T.S6 + 10, T.flow6_nbuckets) * (kFlow6BucketWords * T.flow6_slots);
+        hit = flow6_probe(p, k, tag, rhi, rlo);
+        if (!hit && T.flow6_slots == 2) hit = flow6_probe(p + kFlow6BucketWords, k, tag, rhi, rlo);
     }
     return hit;
 }

@@ -50,10 +50,11 @@ constexpr uint32_t kResMissHi = (SFC_ACT_TO_CP << 24) | (SFC_NF_NONE << 16);
 constexpr uint32_t kResMissLo = 0;
 
 // ---------------------------------------------------------------- flow table -------------
-// Cuckoo table, ONE slot per bucket, d = 2 or 3 bucket choices.  An IPv4 bucket is exactly one
-// 32-byte sector (one LDG.256, one L2/DRAM sector per probe); an IPv6 bucket is 64 bytes.
-//   v4 bucket words: [sip, dip, ports, tag, res_hi, res_lo, 0, 0]
-//   v6 bucket words: [sip0..3, dip0..3, ports, tag, res_hi, res_lo, 0, 0, 0, 0]
+// Cuckoo table, d = 2 or 3 bucket choices, one slot per bucket (two for tables that only fit in L2 when
+// packed, see build_cuckoo).  An IPv4 slot is exactly one 32-byte sector (one LDG.256, one L2/DRAM sector
+// per probe); an IPv6 slot is 64 bytes.
+//   v4 slot words: [sip, dip, ports, tag, res_hi, res_lo, 0, 0]
+//   v6 slot words: [sip0..3, dip0..3, ports, tag, res_hi, res_lo, 0, 0, 0, 0]
 // tag = proto | vlan<<8 | 0x80000000 (the top bit marks an occupied slot; empty slots are zero).
 constexpr uint32_t kSlotValid = 0x80000000u;
 constexpr int kFlow4BucketWords = 8;
@@ -61,6 +62,8 @@ constexpr int kFlow6BucketWords = 16;
 constexpr int kFlow4BucketBytes = 32;
 constexpr int kFlow6BucketBytes = 64;
 constexpr int kMaxHashes = 3;
+constexpr uint64_t kFlowL2ResidentBytes = 48ull << 20;  // measured on B200: a table up to ~42 MB stays in L2 beside the stream
+constexpr uint64_t kFlowDenseLoadPct = 80;              // two-slot buckets, two choices: threshold ~0.89
 constexpr int kFlow4SeedWords = 10;  // 4 for the fold, 2 per bucket choice
 constexpr int kFlow6SeedWords = 16;  // 10 for the fold, 2 per bucket choice
 
@@ -172,7 +175,7 @@ constexpr uint16_t kAclNeedG1 = 1u << 12, kAclNeedG2 = 1u << 13, kAclRankMask = 
 
 // ---------------------------------------------------------------- image ------------------
 constexpr uint64_t kImageMagic = 0x3130434653303042ull;  // "B00SFC01"
-constexpr uint32_t kImageVersion = 9;
+constexpr uint32_t kImageVersion = 10;
 constexpr size_t kImageAlign = 256;
 
 struct ImageHeader {
@@ -207,6 +210,10 @@ struct ImageHeader {
 
     uint64_t lpm4_tail_off, lpm6_tail_off;  // LpmTail records
     uint32_t lpm4_ntails, lpm6_ntails;
+
+    // slots per flow bucket: 1 (one sector per probe: tiny and huge tables) or 2 (dense tables that fit
+    // in L2 only when packed); a table is nbuckets * slots slots, slot s of bucket b at index b * slots + s
+    uint32_t flow4_slots, flow6_slots;
 };
 static_assert(sizeof(ImageHeader) <= 512, "image header grew past its reserved 512 bytes");
 constexpr size_t kImageHeaderBytes = 512;

@@ -199,22 +199,45 @@ bool FlowTable::insert(const uint32_t* rec, std::vector<uint32_t>* dirty) {
     for (int kick = 0; kick < 4000; ++kick) {
         uint32_t b[kMaxHashes];
         buckets_of(cur, b);
-        for (int j = 0; j < nhash; ++j) {
-            uint32_t* p = tab + (size_t)b[j] * BW;
-            if (!(p[TAG] & kSlotValid)) {
-                memcpy(p, cur, 4 * BW);
-                if (dirty) dirty->push_back(b[j]);
-                return true;
+        for (int j = 0; j < nhash; ++j)
+            for (int sl = 0; sl < slots; ++sl) {
+                const uint32_t idx = b[j] * (uint32_t)slots + (uint32_t)sl;
+                uint32_t* p = tab + (size_t)idx * BW;
+                if (!(p[TAG] & kSlotValid)) {
+                    memcpy(p, cur, 4 * BW);
+                    if (dirty) dirty->push_back(idx);
+                    return true;
+                }
+            }
+        // Every candidate slot is taken.  Evict, by preference, a resident that is NOT in its first-choice
+        // bucket: it goes home (or a step closer), so the walk drifts towards tables in which a lookup ends
+        // at the first probe.  Failing that, a random resident as in plain random-walk cuckoo insertion.
+        rng = mix64(rng + kGamma);
+        uint32_t idx = 0xFFFFFFFFu;
+        int j = 0;
+        for (int jj = 0; jj < nhash && idx == 0xFFFFFFFFu; ++jj) {
+            if (b[jj] == came_from) continue;
+            for (int sl = 0; sl < slots; ++sl) {
+                const uint32_t cand = b[jj] * (uint32_t)slots + (uint32_t)sl;
+                uint32_t hb[kMaxHashes];
+                buckets_of(tab + (size_t)cand * BW, hb);
+                if (hb[0] != b[jj] && (rng >> (8 + sl)) % 8 != 0) {  // a little randomness keeps walks from cycling
+                    idx = cand;
+                    j = jj;
+                    break;
+                }
             }
         }
-        rng = mix64(rng + kGamma);
-        int j = (int)(rng % (uint64_t)nhash);
-        if (b[j] == came_from) j = (j + 1) % nhash;
-        uint32_t* p = tab + (size_t)b[j] * BW;
+        if (idx == 0xFFFFFFFFu) {
+            j = (int)(rng % (uint64_t)nhash);
+            if (b[j] == came_from) j = (j + 1) % nhash;
+            idx = b[j] * (uint32_t)slots + (uint32_t)((rng >> 32) % (uint64_t)slots);
+        }
+        uint32_t* p = tab + (size_t)idx * BW;
         memcpy(tmp, p, 4 * BW);
         memcpy(p, cur, 4 * BW);
         memcpy(cur, tmp, 4 * BW);
-        if (dirty) dirty->push_back(b[j]);
+        if (dirty) dirty->push_back(idx);
         came_from = b[j];
     }
     return false;  // the caller rebuilds the table (new seed / more buckets)
@@ -224,25 +247,27 @@ bool FlowTable::erase(const uint32_t* rec, std::vector<uint32_t>* dirty) {
     const int BW = words(), TAG = tag_index();
     uint32_t b[kMaxHashes];
     buckets_of(rec, b);
-    for (int j = 0; j < nhash; ++j) {
-        uint32_t* p = tab + (size_t)b[j] * BW;
-        if ((p[TAG] & kSlotValid) && p[TAG] == rec[TAG] && !memcmp(p, rec, 4 * TAG)) {  // key words precede the tag
-            memset(p, 0, 4 * BW);
-            if (dirty) dirty->push_back(b[j]);
-            return true;
+    for (int j = 0; j < nhash; ++j)
+        for (int sl = 0; sl < slots; ++sl) {
+            const uint32_t idx = b[j] * (uint32_t)slots + (uint32_t)sl;
+            uint32_t* p = tab + (size_t)idx * BW;
+            if ((p[TAG] & kSlotValid) && p[TAG] == rec[TAG] && !memcmp(p, rec, 4 * TAG)) {  // key words precede the tag
+                memset(p, 0, 4 * BW);
+                if (dirty) dirty->push_back(idx);
+                return true;
+            }
         }
-    }
     return false;
 }
 
 uint32_t FlowTable::count_first() const {
     const int BW = words(), TAG = tag_index();
     uint32_t n = 0, b[kMaxHashes];
-    for (uint32_t i = 0; i < nbuckets; ++i) {
+    for (uint64_t i = 0; i < (uint64_t)nbuckets * slots; ++i) {
         const uint32_t* p = tab + (size_t)i * BW;
         if (!(p[TAG] & kSlotValid)) continue;
         buckets_of(p, b);
-        n += b[0] == i;
+        n += b[0] == (uint32_t)(i / slots);
     }
     return n;
 }
@@ -267,24 +292,34 @@ struct Blob {
 
 // ---- cuckoo ------------------------------------------------------------------------------
 bool build_cuckoo(Blob& blob, const RuleStore& rs, bool v6, const std::vector<const FlowRec*>& recs, uint64_t& off,
-                  uint32_t& nbuckets, uint64_t& seed_out, uint32_t& first_out, std::string& err) {
+                  uint32_t& nbuckets, uint32_t& slots_out, uint64_t& seed_out, uint32_t& first_out, std::string& err) {
     const int BW = v6 ? kFlow6BucketWords : kFlow4BucketWords;
     size_t n = recs.size();
     int nhash = rs.flow_hashes;
     int max_load = nhash == 2 ? 45 : 85;
     int load_pct = std::min(std::max(rs.flow_load_pct, 5), max_load);
-    uint64_t nb = std::max<uint64_t>(8, (n * 100 + (uint64_t)load_pct - 1) / (uint64_t)load_pct);
+    // Slots per bucket.  One slot = one sector per probe, which is what counts when the table lives in
+    // DRAM (B200 sustains ~50 G random sectors/s there whatever their size: tools/randgather.cu) and
+    // costs nothing when it is small; it is the default.  Two slots at 80 % load (option "flow_slots" = 2)
+    // halve the footprint and pay off in one narrow case — uniform traffic over 1-2 Mi IPv4 flows, where
+    // the smaller table is still largely in L2 (2 Mi flows: 19.6 vs 24.3 us per Mi packets) — but lose
+    // on skewed traffic, whose hot buckets sit in L2 either way (configs[2]: 28.8 vs 22.2 us).
+    int slots = rs.flow_slots == 2 ? 2 : 1;
+    if (slots == 2) load_pct = std::max(load_pct, (int)kFlowDenseLoadPct);
+    slots_out = (uint32_t)slots;
+    uint64_t nb = std::max<uint64_t>(8, (n * 100 + (uint64_t)load_pct * slots - 1) / ((uint64_t)load_pct * slots));
     std::vector<uint8_t> nf(SFC_MAX_PORTS, (uint8_t)SFC_NF_NONE);
     for (uint32_t p = 0; p < SFC_MAX_PORTS; ++p) nf[p] = nf_of_port(rs, p);
     for (int grow = 0; grow < 6; ++grow, nb = nb + nb / 8 + 1) {
         if (nb > 0xFFFFFFF0ull) break;
         for (int attempt = 0; attempt < 4; ++attempt) {
             size_t start = blob.img.size();
-            off = blob.reserve((size_t)nb * BW * 4, 0x00);
+            off = blob.reserve((size_t)nb * slots * BW * 4, 0x00);
             FlowTable c;
             c.v6 = v6;
             c.tab = blob.at<uint32_t>(off);
             c.nbuckets = (uint32_t)nb;
+            c.slots = slots;
             c.nhash = nhash;
             uint64_t seed = mix64(0x5FC0C0DEull + 977ull * attempt + 31ull * grow + (v6 ? 7ull : 0ull));
             expand_seed(seed, c.S, v6 ? kFlow6SeedWords : kFlow4SeedWords);
@@ -706,8 +741,8 @@ bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& imag
     H.flow4_count = (uint32_t)f4.size();
     H.flow6_count = (uint32_t)f6.size();
     H.flow4_nhash = H.flow6_nhash = (uint32_t)rs.flow_hashes;
-    if (!build_cuckoo(blob, rs, false, f4, H.flow4_off, H.flow4_nbuckets, H.flow4_seed, H.flow4_first, err)) return false;
-    if (!build_cuckoo(blob, rs, true, f6, H.flow6_off, H.flow6_nbuckets, H.flow6_seed, H.flow6_first, err)) return false;
+    if (!build_cuckoo(blob, rs, false, f4, H.flow4_off, H.flow4_nbuckets, H.flow4_slots, H.flow4_seed, H.flow4_first, err)) return false;
+    if (!build_cuckoo(blob, rs, true, f6, H.flow6_off, H.flow6_nbuckets, H.flow6_slots, H.flow6_seed, H.flow6_first, err)) return false;
 
     // L2 steering: resolve OpenFlow priorities per match, exact and wildcard apart
     {
@@ -774,8 +809,9 @@ const char* validate_image(const uint8_t* img, size_t len) {
     if (H.total_bytes != len || H.header_bytes != kImageHeaderBytes)
         return "image: size field does not match the buffer length";
     auto inside = [&](uint64_t off, uint64_t bytes) { return off >= kImageHeaderBytes && off + bytes <= len; };
-    bool ok = inside(H.flow4_off, (uint64_t)H.flow4_nbuckets * kFlow4BucketBytes) &&
-              inside(H.flow6_off, (uint64_t)H.flow6_nbuckets * kFlow6BucketBytes) &&
+    bool ok = (H.flow4_slots == 1 || H.flow4_slots == 2) && (H.flow6_slots == 1 || H.flow6_slots == 2) &&
+              inside(H.flow4_off, (uint64_t)H.flow4_nbuckets * H.flow4_slots * kFlow4BucketBytes) &&
+              inside(H.flow6_off, (uint64_t)H.flow6_nbuckets * H.flow6_slots * kFlow6BucketBytes) &&
               inside(H.l2x_off, ((uint64_t)H.l2x_mask + 1) * sizeof(L2Entry)) &&
               ((H.l2x_mask & (H.l2x_mask + 1)) == 0) && inside(H.l2w_off, (uint64_t)H.l2w_n * sizeof(L2Wild)) &&
               inside(H.lpm4_root_off, 65536 * 4) && inside(H.lpm4_nodes_off, (uint64_t)H.lpm4_nnodes * 1024) &&

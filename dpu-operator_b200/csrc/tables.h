@@ -71,8 +71,9 @@ class FlowIndex {
 // (sfc_commit's incremental path) instead of rebuilding and re-uploading the whole image.
 struct FlowTable {
     bool v6 = false;
-    uint32_t* tab = nullptr;  // nbuckets * words() u32
+    uint32_t* tab = nullptr;  // nbuckets * slots slots of words() u32; slot s of bucket b = b * slots + s
     uint32_t nbuckets = 0;
+    int slots = 1;
     int nhash = 2;
     uint32_t S[16] = {0};
     uint64_t rng = 0x1234567ull;
@@ -80,7 +81,7 @@ struct FlowTable {
     int words() const { return v6 ? kFlow6BucketWords : kFlow4BucketWords; }
     int tag_index() const { return v6 ? 9 : 3; }
     void buckets_of(const uint32_t* rec, uint32_t* b) const;
-    // rec = one bucket image (see encode()); every bucket written is appended to *dirty if given
+    // rec = one slot image (see encode()); the index of every slot written is appended to *dirty if given
     bool insert(const uint32_t* rec, std::vector<uint32_t>* dirty);
     bool erase(const uint32_t* rec, std::vector<uint32_t>* dirty);
     uint32_t count_first() const;
@@ -117,6 +118,7 @@ struct RuleStore {
     // knobs
     int flow_load_pct = 40;
     int flow_hashes = 2;
+    int flow_slots = 0;  // slots per flow bucket: 2 = dense two-slot buckets (see build_cuckoo), anything else = 1
 
     void clear_rules();
 };

@@ -431,3 +431,24 @@ def test_two_threads_two_streams_share_one_handle(torch_cuda):
     for i in range(2):
         w = t.from_numpy(want[i * n:(i + 1) * n].view(np.int64).copy()).cuda()
         assert bool((res[i] == w).all()), f"thread {i}: some launch produced different results"
+
+
+def test_two_slot_dense_tables(torch_cuda):
+    """Option flow_slots = 2: dense two-slot buckets for both families; same answers, smaller table."""
+    sizes = {}
+    for slots in (1, 2):
+        dp = sfc.Dataplane(0)
+        dp.set_option("flow_slots", slots)
+        sc = Scenario(dp)
+        topo = sc.build_chain(8, 3)
+        spec = config3_spec(n_flows=300000, n_ports=topo["n_ports"])
+        install_flows(sc, spec)
+        dp.commit()
+        sizes[slots] = dp.table_size
+        hdr, ports = gen_dev(torch_cuda, dp, spec, 0, 1 << 19)
+        got = classify_dev(torch_cuda, dp, hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), consts.F_COUNTERS)
+        want, cnt = sc.orc.classify(hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), counters=True)
+        assert_same(got, want, hdr.cpu().numpy())
+        assert np.array_equal(dp.counters_read(), cnt)
+        assert (sfc.result_fields(got)[3] == consts.STAGE_FLOW).mean() > 0.5
+    assert sizes[2] < 0.6 * sizes[1]

@@ -27,13 +27,13 @@ def expand_seed(seed, n):
 
 
 class Image:
-    """Field offsets follow struct ImageHeader (version 9)."""
+    """Field offsets follow struct ImageHeader (version 10)."""
 
     def __init__(self, img: np.ndarray):
         self.b = img.tobytes()
         u = lambda fmt, off: struct.unpack_from("<" + fmt, self.b, off)  # noqa: E731
         magic, ver, hb, total, epoch = u("QIIQQ", 0)
-        assert magic == 0x3130434653303042 and ver == 9 and hb == 512 and total == len(self.b)
+        assert magic == 0x3130434653303042 and ver == 10 and hb == 512 and total == len(self.b)
         o = 32
         self.f4_off, self.f4_seed, self.f4_nb, self.f4_nh, self.f4_cnt, self.f4_first = u("QQIIII", o); o += 32
         self.f6_off, self.f6_seed, self.f6_nb, self.f6_nh, self.f6_cnt, self.f6_first = u("QQIIII", o); o += 32
@@ -44,7 +44,8 @@ class Image:
         self.acl_nrules, self.acl_nentries, self.acl_nleaf, self.acl_ntrees = u("IIII", o); o += 16
         roots = u("32I", o); o += 128
         self.acl_roots = [roots[4 * i: 4 * i + 4] for i in range(8)]
-        self.lpm4_tail_off, self.lpm6_tail_off, self.lpm4_ntails, self.lpm6_ntails = u("QQII", o)
+        self.lpm4_tail_off, self.lpm6_tail_off, self.lpm4_ntails, self.lpm6_ntails = u("QQII", o); o += 24
+        self.f4_slots, self.f6_slots = u("II", o)
 
     def u32(self, off, n):
         return np.frombuffer(self.b, dtype="<u4", count=n, offset=off)
@@ -125,9 +126,10 @@ class Image:
             F = ((x ^ S[4 + 2 * j]) * (y ^ S[5 + 2 * j])) & M64
             h = (F & 0xFFFFFFFF) ^ (F >> 32)
             b = (h * self.f4_nb) >> 32
-            s = self.u32(self.f4_off + b * 32, 8)
-            if (int(s[0]), int(s[1]), int(s[2]), int(s[3])) == (sip, dip, ports, meta20 | 0x80000000):
-                return (int(s[4]) << 32) | int(s[5]), j
+            for sl in range(self.f4_slots):
+                s = self.u32(self.f4_off + (b * self.f4_slots + sl) * 32, 8)
+                if (int(s[0]), int(s[1]), int(s[2]), int(s[3])) == (sip, dip, ports, meta20 | 0x80000000):
+                    return (int(s[4]) << 32) | int(s[5]), j
         return None, None
 
 
@@ -190,13 +192,16 @@ def test_acl_forest_on_the_handmade_rules():
             assert r is None or r >> 31 == 0
 
 
-def test_every_ipv4_flow_sits_in_one_of_its_buckets():
+@pytest.mark.parametrize("slots", [1, 2])
+def test_every_ipv4_flow_sits_in_one_of_its_buckets(slots):
     sc = Scenario(sfc.Dataplane(-1))
+    sc.dp.set_option("flow_slots", slots)
     spec = config3_spec(n_flows=20000, v6_permille=0, n_ports=8)
     install_flows(sc, spec)
     sc.dp.commit()
     img = Image(sc.dp.table_export())
-    assert img.f4_cnt == 20000 and img.f4_nb >= 20000 / 0.45
+    assert img.f4_cnt == 20000 and img.f4_slots == slots
+    assert img.f4_nb >= 20000 / 0.45 if slots == 1 else 20000 / 2 / 0.86 <= img.f4_nb <= 20000 / 2 / 0.7
     keys, acts = sfc.gen_flows(spec, 0, 20000)
     first = 0
     for i in range(0, 20000, 7):
@@ -206,7 +211,7 @@ def test_every_ipv4_flow_sits_in_one_of_its_buckets():
         assert res is not None, f"flow {i} is not where the hash says"
         assert res & 0x0FFFFFFF == i and (res >> 28) & 0xF == consts.STAGE_FLOW and res >> 56 == int(acts[i]["action"])
         first += j == 0
-    assert first / len(range(0, 20000, 7)) > 0.6  # most flows answer on the first probe
+    assert first / len(range(0, 20000, 7)) > 0.6  # most flows answer in their first bucket
     assert abs(img.f4_first / 20000 - first / len(range(0, 20000, 7))) < 0.05  # header statistic is honest
 
 

@@ -14,8 +14,10 @@ def _flow4_probe(img, k):
     return img.flow4(sip, dip, (int(k["sport"]) << 16) | int(k["dport"]), int(k["proto"]) | (int(k["vlan"]) << 8))[0]
 
 
-def test_incremental_commit_patches_the_image_in_place():
+@pytest.mark.parametrize("slots", [1, 2])
+def test_incremental_commit_patches_the_image_in_place(slots):
     dp = sfc.Dataplane(-1)
+    dp.set_option("flow_slots", slots)
     spec = config3_spec(n_flows=30000, v6_permille=0, n_ports=8)
     keys, acts = sfc.gen_flows(spec, 0, 30000)
     dp.flow_add_bulk(keys[:20000], acts[:20000])
@@ -23,16 +25,16 @@ def test_incremental_commit_patches_the_image_in_place():
     assert (dp.stat("full_commits"), dp.stat("incremental_commits")) == (1, 0)
     size0, e0 = dp.table_size, dp.table_epoch
     # churn: 3000 new flows, 2000 old ones gone — flows only, so no rebuild
+    for k in keys[:4000:2]:  # deletes first: a two-slot table is built at 80 % load and has little headroom
+        dp.flow_del(k)
     first = dp.flow_add_bulk(keys[20000:23000], acts[20000:23000])
     assert first == 20000
-    for k in keys[:4000:2]:
-        dp.flow_del(k)
     dp.commit()
     assert (dp.stat("full_commits"), dp.stat("incremental_commits")) == (1, 1)
-    assert 5000 <= dp.stat("patched_buckets") <= 8000  # one bucket per edit plus a few cuckoo moves
+    assert 5000 <= dp.stat("patched_buckets") <= (8000 if slots == 1 else 14000)  # one slot per edit plus the cuckoo moves (more at 80 % load)
     assert dp.table_size == size0 and dp.table_epoch == e0 + 1
     img = Image(dp.table_export())
-    assert img.f4_cnt == 21000
+    assert img.f4_cnt == 21000 and img.f4_slots == slots
     for i in list(range(1, 4000, 2)) + list(range(4000, 23000, 37)):  # alive
         r = _flow4_probe(img, keys[i])
         assert r is not None and r & 0x0FFFFFFF == i, i
@@ -80,9 +82,11 @@ def test_flow_index_survives_heavy_delete_churn():
 
 
 @pytest.mark.gpu
-def test_flow_churn_between_launches_on_the_gpu(torch_cuda):
+@pytest.mark.parametrize("slots", [1, 2])
+def test_flow_churn_between_launches_on_the_gpu(torch_cuda, slots):
     torch = torch_cuda
     dp = sfc.Dataplane(0)
+    dp.set_option("flow_slots", slots)
     sc = Scenario(dp)
     topo = sc.build_chain(8, 2)
     spec = config3_spec(n_flows=120000, n_ports=topo["n_ports"])
@@ -116,6 +120,9 @@ def test_flow_churn_between_launches_on_the_gpu(torch_cuda):
         want = sc.orc.classify(hdr, ports, threads=8)
         bad = int((got != want).sum())
         assert bad == 0, f"round {rnd}: {bad} results differ after incremental commit"
-    assert dp.stat("incremental_commits") == 6 and dp.stat("full_commits") == 1
+    if slots == 1:
+        assert dp.stat("incremental_commits") == 6 and dp.stat("full_commits") == 1
+    else:  # built at 80 % load: the net growth of 1000 flows a round forces a rebuild along the way
+        assert dp.stat("incremental_commits") + dp.stat("full_commits") == 7 and dp.stat("incremental_commits") >= 4
     hits = (sfc.result_fields(got)[3] == consts.STAGE_FLOW).mean()
     assert 0.3 < hits < 0.9
