@@ -14,6 +14,7 @@ VARIANTS = [(0, 0), (64, 4), (128, 2), (128, 3), (256, 2), (256, 3), (256, 4), (
 def setup(mode):
     dp = sfc.Dataplane(0)
     dp.set_option("flow_slots", int(os.environ.get("SFC_SLOTS", "0")))
+    dp.set_option("flow_load_pct", int(os.environ.get("SFC_LOAD", "40")))
     if mode == "empty":
         spec = sfc.make_gen_spec(n_flows=1024, hit_permille=900)
     elif mode == "cfg2":
