@@ -39,7 +39,9 @@ template <bool A>
 constexpr int stages_for() { return A ? kStagesAcl : kStages; }
 constexpr int kTicketRing = 256;     // a launch uses slot seq % 256 (so up to 256 launches may be in flight); slots are 32 bytes apart and self-resetting
 constexpr int kTicketStride = 8;     // u32 words per slot: {draw counter, finished producers, pad}
-constexpr size_t kHostChunk = 1u << 18;  // packets per pipelined chunk in sfc_classify_host
+constexpr size_t kHostChunk = 1u << 18;  // largest chunk of sfc_classify_host's pipeline (size of its device buffers)
+constexpr size_t kHostChunkDefault = 1u << 18;
+constexpr int kHostBufs = 4, kHostBufsDefault = 2;
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -66,11 +68,14 @@ struct sfc_handle {
     int probe_mode = -1;  // option "flow_probe_mode": -1 auto, else kProbe* bits
     uint32_t* d_tickets = nullptr;  // ring of kTicketRing tile-ticket counters (scratch of the classify kernel)
     // sfc_classify_host staging
-    cudaStream_t hs[2] = {nullptr, nullptr};
-    cudaEvent_t ev[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
-    uint8_t* d_hdr[2] = {nullptr, nullptr};
-    uint16_t* d_port[2] = {nullptr, nullptr};
-    uint64_t* d_res[2] = {nullptr, nullptr};
+    cudaStream_t hs[kHostBufs] = {};
+    cudaEvent_t ev[kHostBufs][2] = {};
+    uint8_t* d_hdr[kHostBufs] = {};
+    uint16_t* d_port[kHostBufs] = {};
+    uint64_t* d_res[kHostBufs] = {};
+    size_t host_chunk = kHostChunkDefault;  // option "host_chunk": packets per pipelined chunk
+    int host_bufs = kHostBufsDefault;       // option "host_bufs": chunks in flight
+    bool host_timing = false;               // option "host_timing": measure kernel time for sfc_last_kernel_ms
     float last_kernel_ms = -1.f;
     // host shadows of the committed flow tables + staging for incremental commits
     FlowTable shadow4, shadow6;
@@ -400,7 +405,7 @@ int sfc_destroy(sfc_handle* h) {
     if (h->h_patch) cudaFreeHost(h->h_patch);
     if (h->d_patch) cudaFree(h->d_patch);
     if (h->patch_done) cudaEventDestroy(h->patch_done);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kHostBufs; ++i) {
         if (h->d_hdr[i]) cudaFree(h->d_hdr[i]);
         if (h->d_port[i]) cudaFree(h->d_port[i]);
         if (h->d_res[i]) cudaFree(h->d_res[i]);
@@ -426,6 +431,20 @@ int sfc_set_option(sfc_handle* h, const char* name, long value) {
         if (value < 2 || value > kMaxHashes) return fail(h, -EINVAL, "flow_hashes must be 2 or 3");
         h->rs.other_dirty = true;
         h->rs.flow_hashes = (int)value;
+        return 0;
+    }
+    if (!strcmp(name, "host_chunk")) {  // packets per chunk of sfc_classify_host's copy/classify/copy pipeline
+        if (value < 1024 || (size_t)value > kHostChunk) return fail(h, -EINVAL, "host_chunk must be 1024..%zu", kHostChunk);
+        h->host_chunk = (size_t)value;
+        return 0;
+    }
+    if (!strcmp(name, "host_timing")) {
+        h->host_timing = value != 0;
+        return 0;
+    }
+    if (!strcmp(name, "host_bufs")) {
+        if (value < 2 || value > kHostBufs) return fail(h, -EINVAL, "host_bufs must be 2..%d", kHostBufs);
+        h->host_bufs = (int)value;
         return 0;
     }
     if (!strcmp(name, "flow_slots")) {  // slots per flow bucket: 0 / 1 = one (default), 2 = dense two-slot buckets
@@ -1021,7 +1040,7 @@ int sfc_classify_host(sfc_handle* h, const void* hdr, const uint16_t* in_port, u
     if (!hdr || !in_port || !result) return fail(h, -EINVAL, "sfc_classify_host: null buffer");
     DeviceGuard g(h->device);
     if (!h->hs[0]) {
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < kHostBufs; ++i) {
             CUDA_TRY(h, cudaStreamCreateWithFlags(&h->hs[i], cudaStreamNonBlocking));
             CUDA_TRY(h, cudaEventCreate(&h->ev[i][0]));
             CUDA_TRY(h, cudaEventCreate(&h->ev[i][1]));
@@ -1030,34 +1049,38 @@ int sfc_classify_host(sfc_handle* h, const void* hdr, const uint16_t* in_port, u
             CUDA_TRY(h, cudaMalloc(&h->d_res[i], kHostChunk * 8));
         }
     }
+    // Chunks go round a ring of buffers, one stream each: while chunk c is copied in, chunk c-1 is being
+    // classified and chunk c-2 copied out.  What the call cannot hide is the first copy-in and the last
+    // kernel + copy-out, so chunks are kept small enough for that tail to be short.
     const uint8_t* hp = (const uint8_t*)hdr;
-    size_t n_chunks = (n + kHostChunk - 1) / kHostChunk;
+    const size_t chunk = h->host_chunk;
+    const size_t nb = (size_t)h->host_bufs;
+    size_t n_chunks = (n + chunk - 1) / chunk;
     float ms_total = 0.f;
+    const bool timed = h->host_timing;  // two event records per chunk cost ~1.3 % of the call: opt-in
+    auto retire = [&](int b) -> int {  // wait for the chunk that used buffer b, collect its kernel time
+        CUDA_TRY(h, cudaStreamSynchronize(h->hs[b]));
+        float ms = 0.f;
+        if (timed) cudaEventElapsedTime(&ms, h->ev[b][0], h->ev[b][1]);
+        ms_total += ms;
+        return 0;
+    };
     for (size_t c = 0; c < n_chunks; ++c) {
-        int b = (int)(c & 1);
-        size_t off = c * kHostChunk, m = std::min(kHostChunk, n - off);
-        if (c >= 2) {  // buffer b was used by chunk c-2: wait for its D2H, collect its kernel time
-            CUDA_TRY(h, cudaStreamSynchronize(h->hs[b]));
-            float ms = 0.f;
-            cudaEventElapsedTime(&ms, h->ev[b][0], h->ev[b][1]);
-            ms_total += ms;
-        }
+        int b = (int)(c % nb);
+        size_t off = c * chunk, m = std::min(chunk, n - off);
+        if (c >= nb)
+            if (int rc = retire(b)) return rc;
         cudaStream_t st = h->hs[b];
         CUDA_TRY(h, cudaMemcpyAsync(h->d_hdr[b], hp + off * 64, m * 64, cudaMemcpyHostToDevice, st));
         CUDA_TRY(h, cudaMemcpyAsync(h->d_port[b], in_port + off, m * 2, cudaMemcpyHostToDevice, st));
-        CUDA_TRY(h, cudaEventRecord(h->ev[b][0], st));
+        if (timed) CUDA_TRY(h, cudaEventRecord(h->ev[b][0], st));
         int rc = launch_classify(h, h->d_hdr[b], h->d_port[b], h->d_res[b], m, flags, st);
         if (rc) return rc;
-        CUDA_TRY(h, cudaEventRecord(h->ev[b][1], st));
+        if (timed) CUDA_TRY(h, cudaEventRecord(h->ev[b][1], st));
         CUDA_TRY(h, cudaMemcpyAsync(result + off, h->d_res[b], m * 8, cudaMemcpyDeviceToHost, st));
     }
-    for (size_t c = (n_chunks >= 2 ? n_chunks - 2 : 0); c < n_chunks; ++c) {
-        int b = (int)(c & 1);
-        CUDA_TRY(h, cudaStreamSynchronize(h->hs[b]));
-        float ms = 0.f;
-        cudaEventElapsedTime(&ms, h->ev[b][0], h->ev[b][1]);
-        ms_total += ms;
-    }
+    for (size_t c = (n_chunks >= nb ? n_chunks - nb : 0); c < n_chunks; ++c)
+        if (int rc = retire((int)(c % nb))) return rc;
     h->last_kernel_ms = ms_total;
     return 0;
 }

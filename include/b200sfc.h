@@ -320,7 +320,8 @@ void* sfc_counters_device_ptr(sfc_handle* h);
 uint64_t sfc_launch_count(const sfc_handle* h);
 
 /* Device time of the classify kernels launched by the last sfc_classify_host call, in ms
- * (CUDA events on the library's stream); < 0 if none. */
+ * (CUDA events on the library's streams).  Measured only while sfc_set_option(h, "host_timing", 1)
+ * is in force (two event records per chunk are not free); 0 otherwise, < 0 if no call was made. */
 float sfc_last_kernel_ms(const sfc_handle* h);
 
 /* ---------------------------------------------------------------- no-allocation call ---- */

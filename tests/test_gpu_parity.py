@@ -173,7 +173,13 @@ def test_classify_host_matches_device_path(torch_cuda):
     hdr, ports = sfc.gen_packets_host(spec, 5, n)
     got = dp.classify_host(hdr, ports)
     assert_same(got, sc.orc.classify(hdr, ports, threads=8), hdr)
-    assert dp.last_kernel_ms > 0
+    assert dp.last_kernel_ms == 0  # kernel timing is opt-in
+    dp.set_option("host_timing", 1)
+    for bufs, chunk in ((3, 1 << 16), (4, 10000), (2, 1 << 18)):  # other shapes of the staging pipeline
+        dp.set_option("host_bufs", bufs)
+        dp.set_option("host_chunk", chunk)
+        assert np.array_equal(dp.classify_host(hdr, ports), got)
+        assert dp.last_kernel_ms > 0
 
 
 def test_rule_updates_between_commits(torch_cuda):
