@@ -48,4 +48,4 @@ for with_acl in (False, True):
         sfc.classify_static(0, img, hdr.data_ptr(), ports.data_ptr(), res.data_ptr(), n, st); torch.cuda.synchronize()
         assert np.array_equal(res.cpu().numpy().view(np.uint64), sc.orc.classify(hdr_h, port_h)), ("static", with_acl)
     print("variant set ok, acl =", with_acl, flush=True)
-print("sanitize smoke ok")
+print("variant smoke ok")
