@@ -349,7 +349,7 @@ __global__ void gen_kernel(sfc_gen_spec spec, uint64_t first, uint64_t n, uint8_
 // =================================================================== life cycle ==========
 extern "C" {
 
-const char* sfc_version(void) { return "b200sfc 0.7 (image v10)"; }
+const char* sfc_version(void) { return "b200sfc 0.8 (image v11)"; }
 
 int sfc_create(int device_ordinal, sfc_handle** out) {
     if (!out) return -EINVAL;

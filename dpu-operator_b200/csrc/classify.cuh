@@ -353,8 +353,12 @@ __device__ __forceinline__ uint32_t lpm_word_mask(uint32_t len, int i) {  // bit
 }
 // `a` = the destination as four words; an IPv4 address sits in a[0] with a[1..3] = 0, and its trie never
 // has a child below bit 32, so the same walk serves both families.
+// Returns the entry value (next-hop index + 1, 0 = no route).  A hit on a tail record also delivers the high
+// result word (hi_valid), which saves the next-hop load.
 __device__ __forceinline__ uint32_t lpm_lookup(const uint32_t* __restrict__ root, const uint32_t* __restrict__ nodes,
-                                               const LpmTail* __restrict__ tails, const uint32_t* a) {
+                                               const LpmTail* __restrict__ tails, const uint32_t* a, uint32_t& hi,
+                                               bool& hi_valid) {
+    hi_valid = false;
     uint32_t e = __ldg(root + (a[0] >> 16));
 #pragma unroll
     for (int pos = 16; pos < 128; pos += 8) {  // static positions: the address stays in registers
@@ -370,6 +374,8 @@ __device__ __forceinline__ uint32_t lpm_lookup(const uint32_t* __restrict__ root
 #pragma unroll
         for (int i = 0; i < 4; ++i) d |= (a[i] ^ t[i]) & lpm_word_mask(t[4], i);
         e = d ? t[6] : t[5];
+        hi = t[7];
+        hi_valid = d == 0u;
     }
     return e;
 }
@@ -697,12 +703,19 @@ __global__ void __launch_bounds__(TILE + 32, ACL ? SFC_MINB_ACL : SFC_MINB) clas
         if (!done && is_ip) {
             const bool v6 = k.ip_ver == 6;
             if (v6 ? T.lpm6_count : T.lpm4_count) {
+                uint32_t hi;
+                bool hi_valid;
                 const uint32_t e = lpm_lookup(v6 ? T.lpm6_root : T.lpm4_root, v6 ? T.lpm6_nodes : T.lpm4_nodes,
-                                              v6 ? T.lpm6_tails : T.lpm4_tails, k.dip);
+                                              v6 ? T.lpm6_tails : T.lpm4_tails, k.dip, hi, hi_valid);
                 if (e) {
-                    uint2 r = __ldg(reinterpret_cast<const uint2*>((v6 ? T.lpm6_nh : T.lpm4_nh) + (e - 1)));
-                    rhi = r.x;
-                    rlo = r.y;
+                    if (hi_valid) {
+                        rhi = hi;
+                        rlo = res_lo(v6 ? SFC_STAGE_LPM6 : SFC_STAGE_LPM4, e - 1);
+                    } else {
+                        uint2 r = __ldg(reinterpret_cast<const uint2*>((v6 ? T.lpm6_nh : T.lpm4_nh) + (e - 1)));
+                        rhi = r.x;
+                        rlo = r.y;
+                    }
                 }
             }
         }

@@ -135,7 +135,7 @@ struct LpmTail {
     uint32_t len;       // 1..128
     uint32_t match;     // entry value (next-hop index + 1) if the address is inside the prefix
     uint32_t fallback;  // entry value of the covering shorter prefix otherwise (0 = none)
-    uint32_t pad;
+    uint32_t match_hi;  // high result word of `match`, so that a hit needs no next-hop load
 };
 static_assert(sizeof(LpmTail) == 32, "one sector");
 
@@ -175,7 +175,7 @@ constexpr uint16_t kAclNeedG1 = 1u << 12, kAclNeedG2 = 1u << 13, kAclRankMask = 
 
 // ---------------------------------------------------------------- image ------------------
 constexpr uint64_t kImageMagic = 0x3130434653303042ull;  // "B00SFC01"
-constexpr uint32_t kImageVersion = 10;
+constexpr uint32_t kImageVersion = 11;
 constexpr size_t kImageAlign = 256;
 
 struct ImageHeader {

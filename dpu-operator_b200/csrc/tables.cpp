@@ -447,6 +447,10 @@ void build_lpm(Blob& blob, const RuleStore& rs, int af, const std::map<RuleStore
         e.res_hi = res_hi(SFC_ACT_FORWARD, nf_of_port(rs, r.out_port), r.out_port);
         e.res_lo = res_lo(af == 4 ? SFC_STAGE_LPM4 : SFC_STAGE_LPM6, r.id);
     }
+    for (uint32_t i = 0; i < ntails; ++i) {  // a tail hit carries its own result (res_lo = stage | id is computed)
+        LpmTail& t = blob.at<LpmTail>(tail_off)[i];
+        t.match_hi = blob.at<LpmRes>(nh_off)[t.match - 1].res_hi;
+    }
 }
 
 // ---- ACL ---------------------------------------------------------------------------------
@@ -846,7 +850,7 @@ const char* validate_image(const uint8_t* img, size_t len) {
             if (!entry_ok(nodes[i])) return false;
         const LpmTail* tails = (const LpmTail*)(img + tail_off);
         for (uint32_t i = 0; i < ntails; ++i)
-            if (tails[i].len > 128 || (tails[i].match & (kLpmChild | kLpmTail)) || (tails[i].fallback & (kLpmChild | kLpmTail)) ||
+            if (tails[i].len > 128 || tails[i].match == 0 || (tails[i].match & (kLpmChild | kLpmTail)) || (tails[i].fallback & (kLpmChild | kLpmTail)) ||
                 !value_ok(tails[i].match) || !value_ok(tails[i].fallback))
                 return false;
         return true;

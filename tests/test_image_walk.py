@@ -27,13 +27,13 @@ def expand_seed(seed, n):
 
 
 class Image:
-    """Field offsets follow struct ImageHeader (version 10)."""
+    """Field offsets follow struct ImageHeader (version 11)."""
 
     def __init__(self, img: np.ndarray):
         self.b = img.tobytes()
         u = lambda fmt, off: struct.unpack_from("<" + fmt, self.b, off)  # noqa: E731
         magic, ver, hb, total, epoch = u("QIIQQ", 0)
-        assert magic == 0x3130434653303042 and ver == 10 and hb == 512 and total == len(self.b)
+        assert magic == 0x3130434653303042 and ver == 11 and hb == 512 and total == len(self.b)
         o = 32
         self.f4_off, self.f4_seed, self.f4_nb, self.f4_nh, self.f4_cnt, self.f4_first = u("QQIIII", o); o += 32
         self.f6_off, self.f6_seed, self.f6_nb, self.f6_nh, self.f6_cnt, self.f6_first = u("QQIIII", o); o += 32
@@ -111,6 +111,9 @@ class Image:
                 mask = (0xFFFFFFFF << (32 - bits)) & 0xFFFFFFFF if bits else 0
                 diff |= (addr_words[i] ^ int(rec[i])) & mask
             e = int(rec[6]) if diff else int(rec[5])
+            if not diff:  # a tail hit carries the high result word itself
+                hi, lo = self.u32(nh_off + (e - 1) * 8, 2)
+                assert int(rec[7]) == int(hi) and int(lo) == ((consts.STAGE_LPM4 if af == 4 else consts.STAGE_LPM6) << 28 | (e - 1))
         if e == 0:
             return None
         hi, lo = self.u32(nh_off + (e - 1) * 8, 2)
