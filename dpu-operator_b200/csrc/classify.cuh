@@ -380,6 +380,22 @@ __device__ __forceinline__ uint32_t lpm_lookup(const uint32_t* __restrict__ root
     return e;
 }
 
+// COUNTERS: add a thread's byte-packed tallies (at most 255 each) to the CTA's shared counters, one warp
+// reduction and one shared atomic per counter.
+__device__ __forceinline__ void fold_counters(unsigned long long* scnt, uint32_t acc_act, unsigned long long acc_stage,
+                                              int lane) {
+#pragma unroll
+    for (uint32_t a = 0; a < 3; ++a) {
+        const uint32_t c = __reduce_add_sync(0xFFFFFFFFu, (acc_act >> (8u * a)) & 0xFFu);
+        if (lane == 0 && c) atomicAdd(scnt + SFC_CNT_ACTION0 + a, (unsigned long long)c);
+    }
+#pragma unroll
+    for (uint32_t st = 0; st < 7; ++st) {
+        const uint32_t c = __reduce_add_sync(0xFFFFFFFFu, (uint32_t)(acc_stage >> (8u * st)) & 0xFFu);
+        if (lane == 0 && c) atomicAdd(scnt + SFC_CNT_STAGE0 + st, (unsigned long long)c);
+    }
+}
+
 // ------------------------------------------------------------------ the kernel -----------
 template <int TILE, int STAGES, bool ACL>
 struct SmemLayout {
@@ -396,7 +412,7 @@ template <int TILE, int STAGES, bool COUNTERS, bool ACL, bool MULTI = false>
 #ifndef SFC_MINB_ACL
 #define SFC_MINB_ACL 4  // <= 56 registers: four 288-thread CTAs per SM (cfg4: 67 vs 76 us per Mi packets; 5 would spill)
 #endif
-__global__ void __launch_bounds__(TILE + 32, ACL ? SFC_MINB_ACL : SFC_MINB) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
+__global__ void __launch_bounds__(TILE + 32, (ACL || COUNTERS) ? SFC_MINB_ACL : SFC_MINB) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
                                                               const uint16_t* __restrict__ in_port,
                                                               uint64_t* __restrict__ result, uint32_t n,
                                                               uint32_t n_tiles, uint32_t* ticket,
@@ -499,6 +515,8 @@ __global__ void __launch_bounds__(TILE + 32, ACL ? SFC_MINB_ACL : SFC_MINB) clas
     if (ACL) aclq[(tid >> 5) * (kAclKeyRows * 32) + 11 * 32 + lane] = 0u;  // the zero row unused tree bits read
     const uint32_t row_off = (uint32_t)tid * 64u;
     const uint32_t sw = ((uint32_t)tid >> 1) & 3u;
+    uint32_t acc_act = 0u, acc_tiles = 0u;  // COUNTERS: byte a = packets of this thread with action a since the last fold
+    unsigned long long acc_stage = 0ull;    //           byte s = packets decided at stage s
     for (uint32_t it = 0;; ++it) {
         const uint32_t s = it % STAGES, use = it / STAGES;
         mbar_wait(full + s, use & 1);
@@ -723,20 +741,23 @@ __global__ void __launch_bounds__(TILE + 32, ACL ? SFC_MINB_ACL : SFC_MINB) clas
         if (live) stg_result(res_out + pkt, rlo, rhi);
 
         if (COUNTERS) {
-            uint32_t act = rhi >> 24, stage = rlo >> 28;
-#pragma unroll
-            for (uint32_t a = 0; a < 3; ++a) {
-                uint32_t m = __ballot_sync(0xFFFFFFFFu, live && act == a);
-                if (lane == 0 && m) atomicAdd(scnt + SFC_CNT_ACTION0 + a, (unsigned long long)__popc(m));
+            // Per-action / per-stage counts ride in three registers, one byte per counter, and are folded
+            // into the CTA's shared counters every 255 tiles (a ballot per counter per tile cost 20 % of the
+            // kernel on large-table traffic; this costs five instructions).
+            if (live) {
+                acc_act += 1u << (8u * (rhi >> 24));
+                acc_stage += 1ull << (8u * (rlo >> 28));
             }
-#pragma unroll
-            for (uint32_t st = 0; st < 7; ++st) {
-                uint32_t m = __ballot_sync(0xFFFFFFFFu, live && stage == st);
-                if (lane == 0 && m) atomicAdd(scnt + SFC_CNT_STAGE0 + st, (unsigned long long)__popc(m));
+            if (++acc_tiles == 255u) {
+                fold_counters(scnt, acc_act, acc_stage, lane);
+                acc_act = 0u;
+                acc_stage = 0ull;
+                acc_tiles = 0u;
             }
         }
     }
     if (COUNTERS) {
+        fold_counters(scnt, acc_act, acc_stage, lane);
         // consumers only (the producer warp has left): named barrier over the TILE consumer threads
         asm volatile("bar.sync 1, %0;" ::"n"(TILE));
         if (tid < 16 && scnt[tid]) atomicAdd(T.counters + tid, scnt[tid]);
