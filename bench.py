@@ -129,7 +129,7 @@ def run_reference(args, rank, world):
         orc.classify(*pool[i % len(pool)], threads=threads)
     dt = time.perf_counter() - t0
     mpps = args.steps * sample / dt / 1e6
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": mpps, "unit": "Mpps", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
@@ -139,10 +139,30 @@ def run_reference(args, rank, world):
                          "sample": f"{args.steps} steps x {sample} packets (full batch), oracle/sfc_oracle.cpp, {threads} threads"},
         "e2e": {"value": mpps, "unit": "Mpps", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference = CPU oracle port: the Go reference has no software datapath and no Go toolchain exists here",
-    }))
+    })
+
+
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries under us write there too (NCCL prints its version
+    banner to fd 1 on some hosts), so everything but that line is sent to stderr: fd 1 is pointed at fd 2 for the
+    whole run and the line goes to a saved copy of the original descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, line)
 
 
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=2000)
@@ -327,7 +347,7 @@ def main():
         out["cpu_baseline"] = {"value": res_cpu[nthr][0], "unit": "Mpps", "cores": nthr, "kind": "port",
                                "sample": f"the same 1M-packet batch, best of {res_cpu[nthr][1]} passes (~8 s), oracle/sfc_oracle.cpp",
                                "single_thread_mpps": res_cpu[1][0], "bit_exact_vs_gpu": True}
-    print(json.dumps(out))
+    emit(out)
     if world > 1:
         dist.destroy_process_group()
 
