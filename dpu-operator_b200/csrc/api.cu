@@ -61,11 +61,13 @@ struct sfc_handle {
     unsigned long long* d_counters = nullptr;
     std::atomic<uint64_t> launches{0};  // data-plane threads on different streams share the handle
     EncodeTiledFn encode = nullptr;
-    int ctas_per_sm[20] = {0};  // 0-3 shipped variants, 4-12 tune variants, 16-19 multi-batch variants
+    int ctas_per_sm[24] = {0};  // 0-3 shipped variants, 4-12 tune variants, 16-19 multi-batch variants, 20-21 40-register variants
+    bool low_regs = false;      // committed flow tables are too big for L2: use the 40-register variants
     int tune_tile = 0, tune_stages = 0;  // SFC_TUNE=tile,stages (experiments)
     int tune_ctas = 0, tune_carveout = -1;  // cap on resident CTAs per SM / shared-memory carveout percent
     uint32_t flow_first[2] = {0, 0};
     int probe_mode = -1;  // option "flow_probe_mode": -1 auto, else kProbe* bits
+    int occ_mode = -1;    // option "low_regs": -1 by table size, 0 never, 1 always
     uint32_t* d_tickets = nullptr;  // ring of kTicketRing tile-ticket counters (scratch of the classify kernel)
     // sfc_classify_host staging
     cudaStream_t hs[kHostBufs] = {};
@@ -184,6 +186,11 @@ void bind_tables(sfc_handle* h) {
     ImageHeader H;
     cudaMemcpy(&H, h->d_image, sizeof(H), cudaMemcpyDeviceToHost);
     fill_tables(h->T, H, h->d_image, h->d_counters, h->probe_mode);
+    {
+        const uint64_t flow_bytes = (uint64_t)H.flow4_nbuckets * H.flow4_slots * kFlow4BucketBytes * (H.flow4_count ? 1 : 0) +
+                                    (uint64_t)H.flow6_nbuckets * H.flow6_slots * kFlow6BucketBytes * (H.flow6_count ? 1 : 0);
+        h->low_regs = h->occ_mode < 0 ? flow_bytes > kFlowL2ResidentBytes : h->occ_mode > 0;
+    }
     h->epoch = H.epoch;
     h->flow_first[0] = H.flow4_first;
     h->flow_first[1] = H.flow6_first;
@@ -205,10 +212,10 @@ int install_image_from_host(sfc_handle* h, const uint8_t* img, size_t len) {
     return 0;
 }
 
-template <int TILE, int STAGES, bool C, bool A>
+template <int TILE, int STAGES, bool C, bool A, int OCC = 0>
 int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
                    uint32_t flags, cudaStream_t st) {
-    auto kern = classify_kernel<TILE, STAGES, C, A>;
+    auto kern = classify_kernel<TILE, STAGES, C, A, false, OCC>;
     constexpr int smem = SmemLayout<TILE, STAGES, A>::kBytes;
     if (!h->ctas_per_sm[slot]) {
         CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -317,6 +324,10 @@ int launch_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uin
 #undef SFC_TUNE_CASE
     }
     if (c && a) return launch_variant<kTileAcl, kStagesAcl, true, true>(h, 3, hdr, in_port, result, n, flags, st);
+    if (h->low_regs && !a) {  // probes wait on L2 / DRAM: five CTAs per SM at 40 registers (cfg3: 20.9 vs 22.3 us per Mi)
+        if (c) return launch_variant<kTile, kStages, true, false, 5>(h, 21, hdr, in_port, result, n, flags, st);
+        return launch_variant<kTile, kStages, false, false, 5>(h, 20, hdr, in_port, result, n, flags, st);
+    }
     if (c) return launch_variant<kTile, kStages, true, false>(h, 2, hdr, in_port, result, n, flags, st);
     if (a) return launch_variant<kTileAcl, kStagesAcl, false, true>(h, 1, hdr, in_port, result, n, flags, st);
     return launch_variant<kTile, kStages, false, false>(h, 0, hdr, in_port, result, n, flags, st);
@@ -445,6 +456,13 @@ int sfc_set_option(sfc_handle* h, const char* name, long value) {
     if (!strcmp(name, "host_bufs")) {
         if (value < 2 || value > kHostBufs) return fail(h, -EINVAL, "host_bufs must be 2..%d", kHostBufs);
         h->host_bufs = (int)value;
+        return 0;
+    }
+    if (!strcmp(name, "low_regs")) {  // which register budget the non-ACL kernels run with: -1 by table size, 0 / 1 forced
+        if (value < -1 || value > 1) return fail(h, -EINVAL, "low_regs must be -1, 0 or 1");
+        h->occ_mode = (int)value;
+        h->low_regs = value < 0 ? h->low_regs : value > 0;
+        h->rs.other_dirty = true;  // the size rule is re-evaluated at the next full commit
         return 0;
     }
     if (!strcmp(name, "flow_slots")) {  // slots per flow bucket: 0 / 1 = one (default), 2 = dense two-slot buckets
@@ -1023,6 +1041,7 @@ int sfc_classify_batches(sfc_handle* h, const sfc_batch* batches, uint32_t n_bat
         for (uint32_t k = 0; k < L.count; ++k) L.b[k].row0 = (uint32_t)((batch_hdr[k] - lo) / 64);
         const uint64_t rows = (hi - lo) / 64;
         int rc;
+        // (the multi-batch variants spill at 40 registers and gain nothing from them: always the regular budget)
         if (c && a) rc = launch_multi<true, true>(h, 19, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
         else if (c) rc = launch_multi<true, false>(h, 18, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
         else if (a) rc = launch_multi<false, true>(h, 17, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);

@@ -405,14 +405,16 @@ struct SmemLayout {
                                   STAGES * (int)sizeof(StageInfo) + 1024;
 };
 
-template <int TILE, int STAGES, bool COUNTERS, bool ACL, bool MULTI = false>
+template <int TILE, int STAGES, bool COUNTERS, bool ACL, bool MULTI = false, int OCC = 0>
 #ifndef SFC_MINB
 #define SFC_MINB 1
 #endif
 #ifndef SFC_MINB_ACL
 #define SFC_MINB_ACL 4  // <= 56 registers: four 288-thread CTAs per SM (cfg4: 67 vs 76 us per Mi packets; 5 would spill)
 #endif
-__global__ void __launch_bounds__(TILE + 32, (ACL || COUNTERS) ? SFC_MINB_ACL : SFC_MINB) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
+// OCC = 5: the same code held to 40 registers so that five CTAs share an SM — slower where the table is in L1
+// (more instructions), faster where probes wait on L2 / DRAM (api.cu picks per committed table).
+__global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS) ? SFC_MINB_ACL : SFC_MINB)) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
                                                               const uint16_t* __restrict__ in_port,
                                                               uint64_t* __restrict__ result, uint32_t n,
                                                               uint32_t n_tiles, uint32_t* ticket,
