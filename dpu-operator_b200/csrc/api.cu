@@ -263,10 +263,10 @@ int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_
 
 // One launch over the batches of `L` (already laid out: row0 / tile0 filled in, `rows` = extent of the
 // tensor map in 64-byte records from L.base).
-template <bool C, bool A>
+template <bool C, bool A, int OCC = 0>
 int launch_multi(sfc_handle* h, int slot, const BatchList& L, uint64_t rows, uint32_t n_tiles, uint32_t flags,
                  cudaStream_t st) {
-    auto kern = classify_kernel<kTile, stages_for<A>(), C, A, true>;
+    auto kern = classify_kernel<kTile, stages_for<A>(), C, A, true, OCC>;
     constexpr int smem = SmemLayout<kTile, stages_for<A>(), A>::kBytes;
     if (!h->ctas_per_sm[slot]) {
         CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -1041,8 +1041,8 @@ int sfc_classify_batches(sfc_handle* h, const sfc_batch* batches, uint32_t n_bat
         for (uint32_t k = 0; k < L.count; ++k) L.b[k].row0 = (uint32_t)((batch_hdr[k] - lo) / 64);
         const uint64_t rows = (hi - lo) / 64;
         int rc;
-        // (the multi-batch variants spill at 40 registers and gain nothing from them: always the regular budget)
-        if (c && a) rc = launch_multi<true, true>(h, 19, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
+        if (h->low_regs && !a && !c) rc = launch_multi<false, false, 5>(h, 22, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
+        else if (c && a) rc = launch_multi<true, true>(h, 19, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
         else if (c) rc = launch_multi<true, false>(h, 18, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
         else if (a) rc = launch_multi<false, true>(h, 17, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
         else rc = launch_multi<false, false>(h, 16, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);

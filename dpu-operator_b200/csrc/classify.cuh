@@ -402,7 +402,7 @@ struct SmemLayout {
     static constexpr int kTileBytes = TILE * 64;
     static constexpr int kAclBytes = ACL ? (TILE / 32) * kAclKeyRows * 32 * 4 : 0;
     static constexpr int kBytes = STAGES * kTileBytes + kAclBytes + 2 * STAGES * 8 + 16 * 8 + 32 * 4 + STAGES * 4 + 16 +
-                                  STAGES * (int)sizeof(StageInfo) + 1024;
+                                  STAGES * (int)sizeof(StageInfo) + (TILE / 32) * 8 + 1024;
 };
 
 template <int TILE, int STAGES, bool COUNTERS, bool ACL, bool MULTI = false, int OCC = 0>
@@ -431,6 +431,7 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS) ? SF
     uint32_t* dep_sink = (uint32_t*)(scnt + 16);                       // one word per consumer warp
     uint32_t* tile_of = dep_sink + 32;                                 // tile index held by each stage
     StageInfo* info = (StageInfo*)(((uintptr_t)(tile_of + STAGES) + 15) & ~(uintptr_t)15);
+    uint64_t** wres = (uint64_t**)(info + STAGES);  // MULTI: result base of the tile each consumer warp is working on
 
     const int tid = threadIdx.x;
     constexpr int kConsumerWarps = TILE / 32;
@@ -536,6 +537,10 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS) ? SF
             ports_in = si.in_port;
             res_out = si.result;
             info_dep = si.first ^ si.rows ^ si.raw ^ (uint32_t)(uintptr_t)ports_in ^ (uint32_t)(uintptr_t)res_out;
+            // the result pointer is not needed until the very end of the tile: park it in the warp's own slot
+            // instead of carrying it in two registers through the whole lookup
+            if (lane == 0) wres[tid >> 5] = res_out;
+            __syncwarp();
         } else {
             pkt = tile * TILE + tid;
             live = pkt < n;
@@ -740,6 +745,7 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS) ? SF
             }
         }
 
+        if constexpr (MULTI) res_out = wres[tid >> 5];
         if (live) stg_result(res_out + pkt, rlo, rhi);
 
         if (COUNTERS) {
