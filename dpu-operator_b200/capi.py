@@ -88,6 +88,8 @@ def _load():
         "sfc_classify": (C.c_int, [vp, vp, vp, vp, C.c_size_t, C.c_uint32, vp]),
         "sfc_classify_batches": (C.c_int, [vp, vp, C.c_uint32, C.c_uint32, vp]),
         "sfc_classify_host": (C.c_int, [vp, vp, vp, vp, C.c_size_t, C.c_uint32]),
+        "sfc_classify_host_submit": (C.c_int, [vp, vp, vp, vp, C.c_size_t, C.c_uint32, u64p]),
+        "sfc_classify_host_wait": (C.c_int, [vp, C.c_uint64]),
         "sfc_sync": (C.c_int, [vp, vp]),
         "sfc_counters_read": (C.c_int, [vp, u64p, C.c_size_t]),
         "sfc_counters_reset": (C.c_int, [vp]),
@@ -318,6 +320,15 @@ class Dataplane:
     def classify_host_ptr(self, hdr_ptr: int, in_port_ptr: int, result_ptr: int, n: int, flags: int = 0):
         """Same call with raw host addresses (e.g. pinned torch tensors)."""
         self._chk(lib.sfc_classify_host(self._h, hdr_ptr, in_port_ptr, result_ptr, n, flags))
+
+    def classify_host_submit(self, hdr_ptr: int, in_port_ptr: int, result_ptr: int, n: int, flags: int = 0) -> int:
+        """Queue one batch held in host memory (raw addresses); returns the ticket for classify_host_wait."""
+        t = C.c_uint64(0)
+        self._chk(lib.sfc_classify_host_submit(self._h, hdr_ptr, in_port_ptr, result_ptr, n, flags, C.byref(t)))
+        return t.value
+
+    def classify_host_wait(self, ticket: int = 0xFFFFFFFFFFFFFFFF):
+        self._chk(lib.sfc_classify_host_wait(self._h, ticket))
 
     def sync(self, stream: int = 0):
         self._chk(lib.sfc_sync(self._h, stream))

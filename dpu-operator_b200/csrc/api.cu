@@ -78,6 +78,10 @@ struct sfc_handle {
     size_t host_chunk = kHostChunkDefault;  // option "host_chunk": packets per pipelined chunk
     int host_bufs = kHostBufsDefault;       // option "host_bufs": chunks in flight
     bool host_timing = false;               // option "host_timing": measure kernel time for sfc_last_kernel_ms
+    uint64_t host_seq = 0;                  // chunks submitted so far; chunk k uses ring slot k % host_bufs
+    bool host_busy[kHostBufs] = {};         // slot holds a chunk that has not been waited for
+    uint64_t host_last[kHostBufs] = {};     // number of the chunk last submitted on the slot
+    float host_ms_acc = 0.f;
     float last_kernel_ms = -1.f;
     // host shadows of the committed flow tables + staging for incremental commits
     FlowTable shadow4, shadow6;
@@ -455,6 +459,7 @@ int sfc_set_option(sfc_handle* h, const char* name, long value) {
     }
     if (!strcmp(name, "host_bufs")) {
         if (value < 2 || value > kHostBufs) return fail(h, -EINVAL, "host_bufs must be 2..%d", kHostBufs);
+        if (!h->offline()) sfc_classify_host_wait(h, ~0ull);  // the slot of a chunk number changes with the ring size
         h->host_bufs = (int)value;
         return 0;
     }
@@ -1051,10 +1056,29 @@ int sfc_classify_batches(sfc_handle* h, const sfc_batch* batches, uint32_t n_bat
     return 0;
 }
 
-int sfc_classify_host(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
-                      uint32_t flags) {
+// The host path: chunks of a call go round a ring of staging buffers, one stream each — while chunk c is copied
+// in, chunk c-1 is being classified and chunk c-2 copied out.  Submission and completion are separate so that a
+// caller can queue the next batch before collecting the previous one: then the only thing PCIe ever waits for is
+// the very first copy-in (a lone synchronous call also exposes its last kernel + copy-out).
+namespace {
+int host_retire(sfc_handle* h, int b) {  // wait for the chunk in ring slot b (its buffers may then be reused)
+    if (!h->host_busy[b]) return 0;
+    CUDA_TRY(h, cudaStreamSynchronize(h->hs[b]));
+    h->host_busy[b] = false;
+    if (h->host_timing) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[b][0], h->ev[b][1]);
+        h->host_ms_acc += ms;
+    }
+    return 0;
+}
+}  // namespace
+
+int sfc_classify_host_submit(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
+                             uint32_t flags, uint64_t* ticket) {
     if (!h) return -EINVAL;
     if (h->offline()) return fail(h, -ENODEV, "offline handle: no device (there is no CPU data path)");
+    if (ticket) *ticket = h->host_seq;
     if (n == 0) return 0;
     if (!hdr || !in_port || !result) return fail(h, -EINVAL, "sfc_classify_host: null buffer");
     DeviceGuard g(h->device);
@@ -1068,27 +1092,13 @@ int sfc_classify_host(sfc_handle* h, const void* hdr, const uint16_t* in_port, u
             CUDA_TRY(h, cudaMalloc(&h->d_res[i], kHostChunk * 8));
         }
     }
-    // Chunks go round a ring of buffers, one stream each: while chunk c is copied in, chunk c-1 is being
-    // classified and chunk c-2 copied out.  What the call cannot hide is the first copy-in and the last
-    // kernel + copy-out, so chunks are kept small enough for that tail to be short.
     const uint8_t* hp = (const uint8_t*)hdr;
     const size_t chunk = h->host_chunk;
-    const size_t nb = (size_t)h->host_bufs;
-    size_t n_chunks = (n + chunk - 1) / chunk;
-    float ms_total = 0.f;
     const bool timed = h->host_timing;  // two event records per chunk cost ~1.3 % of the call: opt-in
-    auto retire = [&](int b) -> int {  // wait for the chunk that used buffer b, collect its kernel time
-        CUDA_TRY(h, cudaStreamSynchronize(h->hs[b]));
-        float ms = 0.f;
-        if (timed) cudaEventElapsedTime(&ms, h->ev[b][0], h->ev[b][1]);
-        ms_total += ms;
-        return 0;
-    };
-    for (size_t c = 0; c < n_chunks; ++c) {
-        int b = (int)(c % nb);
-        size_t off = c * chunk, m = std::min(chunk, n - off);
-        if (c >= nb)
-            if (int rc = retire(b)) return rc;
+    for (size_t off = 0; off < n; off += chunk) {
+        const size_t m = std::min(chunk, n - off);
+        const int b = (int)(h->host_seq % (uint64_t)h->host_bufs);
+        if (int rc = host_retire(h, b)) return rc;
         cudaStream_t st = h->hs[b];
         CUDA_TRY(h, cudaMemcpyAsync(h->d_hdr[b], hp + off * 64, m * 64, cudaMemcpyHostToDevice, st));
         CUDA_TRY(h, cudaMemcpyAsync(h->d_port[b], in_port + off, m * 2, cudaMemcpyHostToDevice, st));
@@ -1097,10 +1107,33 @@ int sfc_classify_host(sfc_handle* h, const void* hdr, const uint16_t* in_port, u
         if (rc) return rc;
         if (timed) CUDA_TRY(h, cudaEventRecord(h->ev[b][1], st));
         CUDA_TRY(h, cudaMemcpyAsync(result + off, h->d_res[b], m * 8, cudaMemcpyDeviceToHost, st));
+        h->host_busy[b] = true;
+        h->host_last[b] = h->host_seq++;
     }
-    for (size_t c = (n_chunks >= nb ? n_chunks - nb : 0); c < n_chunks; ++c)
-        if (int rc = retire((int)(c % nb))) return rc;
-    h->last_kernel_ms = ms_total;
+    if (ticket) *ticket = h->host_seq;  // every chunk numbered below this belongs to this call or an earlier one
+    return 0;
+}
+
+int sfc_classify_host_wait(sfc_handle* h, uint64_t ticket) {
+    if (!h) return -EINVAL;
+    if (h->offline()) return fail(h, -ENODEV, "offline handle: no device (there is no CPU data path)");
+    DeviceGuard g(h->device);
+    // A slot whose latest chunk is newer than the ticket was reused since, and reuse waits for the older chunk:
+    // only slots still holding a chunk of the awaited calls need waiting for.
+    for (int b = 0; b < kHostBufs; ++b)
+        if (h->host_busy[b] && h->host_last[b] < ticket)
+            if (int rc = host_retire(h, b)) return rc;
+    return 0;
+}
+
+int sfc_classify_host(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
+                      uint32_t flags) {
+    if (!h) return -EINVAL;
+    h->host_ms_acc = 0.f;
+    uint64_t ticket = 0;
+    if (int rc = sfc_classify_host_submit(h, hdr, in_port, result, n, flags, &ticket)) return rc;
+    if (int rc = sfc_classify_host_wait(h, ticket)) return rc;
+    if (n) h->last_kernel_ms = h->host_ms_acc;
     return 0;
 }
 

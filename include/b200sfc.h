@@ -307,6 +307,14 @@ int sfc_classify_batches(sfc_handle* h, const sfc_batch* batches, uint32_t n_bat
 int sfc_classify_host(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result,
                       size_t n, uint32_t flags);
 
+/* The same in two steps, for a loop that queues batch k+1 before it collects batch k (the copy engines then
+ * never wait for the host).  submit returns once the work is queued and writes a ticket; the three buffers
+ * must stay valid and untouched until sfc_classify_host_wait(h, ticket) returns, which it does once that
+ * call and every earlier one have completed (ticket ~0 = everything).  One caller thread per handle. */
+int sfc_classify_host_submit(sfc_handle* h, const void* hdr, const uint16_t* in_port,
+                             uint64_t* result, size_t n, uint32_t flags, uint64_t* ticket);
+int sfc_classify_host_wait(sfc_handle* h, uint64_t ticket);
+
 /* Block until everything submitted on `cuda_stream` has finished. */
 int sfc_sync(sfc_handle* h, void* cuda_stream);
 

@@ -458,3 +458,28 @@ def test_two_slot_dense_tables(torch_cuda):
         assert np.array_equal(dp.counters_read(), cnt)
         assert (sfc.result_fields(got)[3] == consts.STAGE_FLOW).mean() > 0.5
     assert sizes[2] < 0.6 * sizes[1]
+
+
+def test_host_submit_wait_pipeline(torch_cuda):
+    """sfc_classify_host_submit / _wait: several batches in flight, collected in order, equal to the blocking call."""
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    spec = config2_spec()
+    install_flows(sc, spec)
+    dp.commit()
+    sizes = [300001, 1 << 18, 77, 600000, 1]
+    batches = [sfc.gen_packets_host(spec, 1000 * i, n) for i, n in enumerate(sizes)]
+    want = [dp.classify_host(h, p) for h, p in batches]
+    for bufs in (2, 4):
+        dp.set_option("host_bufs", bufs)
+        hs = [np.ascontiguousarray(h) for h, _ in batches]
+        ps = [np.ascontiguousarray(p) for _, p in batches]
+        outs = [np.zeros(n, dtype=np.uint64) for n in sizes]
+        tickets = [dp.classify_host_submit(h.ctypes.data, p.ctypes.data, o.ctypes.data, o.size) for h, p, o in zip(hs, ps, outs)]
+        assert tickets == sorted(tickets)
+        dp.classify_host_wait(tickets[1])  # the first two calls are complete, later ones may not be
+        assert np.array_equal(outs[0], want[0]) and np.array_equal(outs[1], want[1])
+        dp.classify_host_wait()  # everything
+        for o, w in zip(outs, want):
+            assert np.array_equal(o, w)
+    assert_same(want[0], sc.orc.classify(*batches[0], threads=8))
