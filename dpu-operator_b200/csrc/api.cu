@@ -191,9 +191,14 @@ void bind_tables(sfc_handle* h) {
     cudaMemcpy(&H, h->d_image, sizeof(H), cudaMemcpyDeviceToHost);
     fill_tables(h->T, H, h->d_image, h->d_counters, h->probe_mode);
     {
-        const uint64_t flow_bytes = (uint64_t)H.flow4_nbuckets * H.flow4_slots * kFlow4BucketBytes * (H.flow4_count ? 1 : 0) +
-                                    (uint64_t)H.flow6_nbuckets * H.flow6_slots * kFlow6BucketBytes * (H.flow6_count ? 1 : 0);
-        h->low_regs = h->occ_mode < 0 ? flow_bytes > kFlowL2ResidentBytes : h->occ_mode > 0;
+        // what the probes of one launch range over: flow slots, trie nodes and tail records
+        uint64_t probed = (uint64_t)H.flow4_nbuckets * H.flow4_slots * kFlow4BucketBytes * (H.flow4_count ? 1 : 0) +
+                          (uint64_t)H.flow6_nbuckets * H.flow6_slots * kFlow6BucketBytes * (H.flow6_count ? 1 : 0);
+        if (H.lpm4_count) probed += (uint64_t)H.lpm4_nnodes * 1024 + (uint64_t)H.lpm4_ntails * sizeof(LpmTail);
+        if (H.lpm6_count) probed += (uint64_t)H.lpm6_nnodes * 1024 + (uint64_t)H.lpm6_ntails * sizeof(LpmTail);
+        // measured (profiles/r01_tuning.md): no difference around 20 MB, 5-10 % in favour of 40 registers from 30 MB up,
+        // 7 % against when the table sits in L1
+        h->low_regs = h->occ_mode < 0 ? probed > (24ull << 20) : h->occ_mode > 0;
     }
     h->epoch = H.epoch;
     h->flow_first[0] = H.flow4_first;
