@@ -15,6 +15,7 @@ def setup(mode):
     dp = sfc.Dataplane(0)
     dp.set_option("flow_slots", int(os.environ.get("SFC_SLOTS", "0")))
     dp.set_option("flow_load_pct", int(os.environ.get("SFC_LOAD", "40")))
+    dp.set_option("low_regs", int(os.environ.get("SFC_LOWREGS", "-1")))
     if mode == "empty":
         spec = sfc.make_gen_spec(n_flows=1024, hit_permille=900)
     elif mode == "cfg2":
