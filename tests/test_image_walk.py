@@ -136,6 +136,50 @@ class Image:
         return None, None
 
 
+def _flow6(self, sip, dip, ports, meta20):
+    """sip / dip: four words each.  Mirrors flow6_hash + flow_bucket + the 64-byte slot compare."""
+    S = expand_seed(self.f6_seed, 16)
+    mw = lambda a, b: (a * b) & M64  # noqa: E731
+    P1, P2 = mw(sip[0] ^ S[0], sip[1] ^ S[1]), mw(sip[2] ^ S[2], sip[3] ^ S[3])
+    P3, P4 = mw(dip[0] ^ S[4], dip[1] ^ S[5]), mw(dip[2] ^ S[6], dip[3] ^ S[7])
+    Q = mw(ports ^ S[8], meta20 ^ S[9])
+    lo, hi = (lambda v: v & 0xFFFFFFFF), (lambda v: v >> 32)
+    x = lo(P1) ^ hi(P2) ^ lo(P3) ^ hi(P4) ^ hi(Q)
+    y = hi(P1) ^ lo(P2) ^ hi(P3) ^ lo(P4) ^ lo(Q)
+    for j in range(self.f6_nh):
+        F = mw(x ^ S[10 + 2 * j], y ^ S[11 + 2 * j])
+        b = ((lo(F) ^ hi(F)) * self.f6_nb) >> 32
+        for sl in range(self.f6_slots):
+            s = [int(v) for v in self.u32(self.f6_off + (b * self.f6_slots + sl) * 64, 12)]
+            if s[:4] == list(sip) and s[4:8] == list(dip) and s[8] == ports and s[9] == meta20 | 0x80000000:
+                return (s[10] << 32) | s[11], j
+    return None, None
+
+
+def _l2(self, in_port, mac):
+    """Exact (in_port, dl_dst) first, then the in_port wildcard; returns the result word or None."""
+    key_hi, key_lo = (in_port << 16) | int.from_bytes(mac[:2], "big"), int.from_bytes(mac[2:], "big")
+    if self.l2x_cnt:
+        P = ((key_hi ^ 0x9E3779B1) * (key_lo ^ 0x85EBCA6B)) & M64
+        i = ((P & 0xFFFFFFFF) ^ (P >> 32)) & self.l2x_mask
+        while True:
+            e = [int(v) for v in self.u32(self.l2x_off + i * 16, 4)]
+            if not e[3]:
+                break
+            if e[0] == key_lo and e[1] == key_hi:
+                return (e[3] << 32) | e[2]
+            i = (i + 1) & self.l2x_mask
+    if self.l2w_cnt and in_port < self.l2w_n:
+        hi, lo = (int(v) for v in self.u32(self.l2w_off + in_port * 8, 2))
+        if hi:
+            return (hi << 32) | lo
+    return None
+
+
+Image.flow6 = _flow6
+Image.l2 = _l2
+
+
 def acl_key(pkt, in_port):
     p = Oracle.parse(pkt)
     w = lambda b: int.from_bytes(b, "big")  # noqa: E731
@@ -278,3 +322,39 @@ def test_import_refuses_images_whose_indices_point_outside_their_tables():
     assert refused(lambda b: put32(b, 8, 8))                                                     # older image version
     with pytest.raises(sfc.SfcError):
         sfc.Dataplane(-1).table_import(good[:-256])                                               # truncated
+
+
+def test_ipv6_flows_and_l2_rules_are_where_the_kernel_will_look():
+    """The two table kinds the other walks do not reach: every IPv6 flow in one of its buckets with the result the
+    API was given, and the chain's L2 steering rules answering like the oracle (exact beats wildcard)."""
+    sc = Scenario(sfc.Dataplane(-1))
+    topo = sc.build_chain(8, 3)
+    spec = config3_spec(n_flows=6000, v6_permille=1000, n_ports=topo["n_ports"])
+    install_flows(sc, spec)
+    sc.dp.commit()
+    img = Image(sc.dp.table_export())
+    assert img.f6_cnt == 6000 and img.f4_cnt == 0
+    keys, acts = sfc.gen_flows(spec, 0, 6000)
+    w4 = lambda b: [int.from_bytes(bytes(b[i:i + 4]), "big") for i in range(0, 16, 4)]  # noqa: E731
+    for i in range(0, 6000, 5):
+        k = keys[i]
+        res, _ = img.flow6(w4(k["src"]), w4(k["dst"]), (int(k["sport"]) << 16) | int(k["dport"]), int(k["proto"]) | (int(k["vlan"]) << 8))
+        assert res is not None and res & 0x0FFFFFFF == i and (res >> 28) & 0xF == consts.STAGE_FLOW and res >> 56 == int(acts[i]["action"]), i
+    # L2: non-IP frames from every port towards every VF MAC and towards an unknown MAC
+    import packets
+    macs = [sfc.gen_mac(v) for v in range(8)] + [bytes.fromhex("0200deadbeef")]
+    frames, in_ports = [], []
+    for port in range(topo["n_ports"]):
+        for m in macs:
+            frames.append(np.frombuffer(packets.eth(m, bytes(6), 0x0806, bytes(28)), np.uint8))
+            in_ports.append(port)
+    want = sc.orc.classify(np.stack(frames), np.array(in_ports, np.uint16))
+    hits = 0
+    for f, port, wv in zip(frames, in_ports, want):
+        got = img.l2(port, bytes(f[:6]))
+        if got is None:
+            assert (int(wv) >> 28) & 0xF == consts.STAGE_MISS
+        else:
+            assert got == int(wv)
+            hits += 1
+    assert hits > len(frames) // 3
