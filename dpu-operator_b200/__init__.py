@@ -18,6 +18,7 @@ from .capi import (  # noqa: F401
     GEN_SPEC_DTYPE,
     LIB_PATH,
     Dataplane,
+    Group,
     SfcError,
     STATIC_AREA_BYTES,
     VspServer,
@@ -35,6 +36,7 @@ from . import consts  # noqa: F401
 
 __all__ = [
     "Dataplane",
+    "Group",
     "SfcError",
     "lib",
     "LIB_PATH",

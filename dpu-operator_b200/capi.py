@@ -91,6 +91,14 @@ def _load():
         "sfc_classify_host_submit": (C.c_int, [vp, vp, vp, vp, C.c_size_t, C.c_uint32, u64p]),
         "sfc_classify_host_wait": (C.c_int, [vp, C.c_uint64]),
         "sfc_sync": (C.c_int, [vp, vp]),
+        "sfc_group_create": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(vp)]),
+        "sfc_group_destroy": (C.c_int, [vp]),
+        "sfc_group_size": (C.c_int, [vp]),
+        "sfc_group_handle": (vp, [vp, C.c_int]),
+        "sfc_group_broadcast_table": (C.c_int, [vp]),
+        "sfc_group_reduce_counters": (C.c_int, [vp]),
+        "sfc_group_last_ms": (C.c_float, [vp, C.c_int]),
+        "sfc_group_last_error": (C.c_char_p, [vp]),
         "sfc_counters_read": (C.c_int, [vp, u64p, C.c_size_t]),
         "sfc_counters_reset": (C.c_int, [vp]),
         "sfc_counters_device_ptr": (vp, [vp]),
@@ -412,6 +420,51 @@ class VspServer:
 
 
 STATIC_AREA_BYTES = 4 << 20
+
+
+class Group:
+    """``sfc_group``: one process driving several GPUs.  ``group[r]`` is the Dataplane of rank r (borrowed: the
+    group owns the handles); rules are staged and committed on ``group[0]`` and replicated with ``broadcast_table``."""
+
+    def __init__(self, n_gpus: int, devices=None):
+        arr = (C.c_int * n_gpus)(*devices) if devices is not None else None
+        g = C.c_void_p()
+        rc = lib.sfc_group_create(n_gpus, arr, C.byref(g))
+        if rc:
+            raise SfcError(rc, "sfc_group_create failed (fewer GPUs than asked for, or NCCL cannot be opened)")
+        self._g = g
+        self.ranks = [Dataplane(devices[r] if devices is not None else r, _borrowed=lib.sfc_group_handle(g, r)) for r in range(n_gpus)]
+
+    def __len__(self):
+        return len(self.ranks)
+
+    def __getitem__(self, r):
+        return self.ranks[r]
+
+    def _chk(self, rc):
+        if rc < 0:
+            raise SfcError(rc, lib.sfc_group_last_error(self._g).decode())
+
+    def broadcast_table(self) -> float:
+        self._chk(lib.sfc_group_broadcast_table(self._g))
+        return lib.sfc_group_last_ms(self._g, 0)
+
+    def reduce_counters(self) -> float:
+        self._chk(lib.sfc_group_reduce_counters(self._g))
+        return lib.sfc_group_last_ms(self._g, 1)
+
+    def close(self):
+        if getattr(self, "_g", None):
+            for d in self.ranks:
+                d._h = None
+            lib.sfc_group_destroy(self._g)
+            self._g = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def classify_static(device: int, image, hdr_ptr: int, in_port_ptr: int, result_ptr: int, n: int, stream: int = 0):

@@ -332,6 +332,30 @@ uint64_t sfc_launch_count(const sfc_handle* h);
  * is in force (two event records per chunk are not free); 0 otherwise, < 0 if no call was made. */
 float sfc_last_kernel_ms(const sfc_handle* h);
 
+/* ---------------------------------------------------------------- several GPUs ----------
+ * One process, several B200s — the shape of a Go VSP.  The path shards by packets:
+ * the table image is replicated, every GPU classifies its own batches with the calls above on
+ * its own handle, and there is no collective on the per-batch path.  The two collectives that
+ * exist run over NCCL (NVLink / NVSwitch), opened with dlopen("libnccl.so.2") at creation:
+ *   sfc_group_broadcast_table  rank 0's committed image -> every other GPU (ncclBroadcast);
+ *   sfc_group_reduce_counters  sum of the SFC_CNT_TOTAL counters over the GPUs, in place on each
+ *                              (ncclAllReduce): every array then holds the total, so reset before
+ *                              counting again.
+ * Rules are staged and committed on rank 0's handle only (sfc_group_handle(g, 0)); the other
+ * handles receive images.  device_ordinals = NULL means GPUs 0 .. n_gpus-1.  Errors: negative
+ * errno, text from sfc_group_last_error; -ENODEV without a GPU, -ENOSYS if NCCL cannot be opened.
+ * sfc_group_last_ms: device time of the last broadcast (which = 0) or all-reduce (which = 1).
+ * No reference counterpart (the reference programs one DPU per VSP process). */
+typedef struct sfc_group sfc_group;
+int sfc_group_create(int n_gpus, const int* device_ordinals, sfc_group** out);
+int sfc_group_destroy(sfc_group* g);
+int sfc_group_size(const sfc_group* g);
+sfc_handle* sfc_group_handle(sfc_group* g, int rank);
+int sfc_group_broadcast_table(sfc_group* g);
+int sfc_group_reduce_counters(sfc_group* g);
+float sfc_group_last_ms(const sfc_group* g, int which);
+const char* sfc_group_last_error(const sfc_group* g);
+
 /* ---------------------------------------------------------------- no-allocation call ---- */
 
 /* Classify without ever allocating.  This entry point has no counterpart in the reference.
