@@ -483,3 +483,36 @@ def test_host_submit_wait_pipeline(torch_cuda):
         for o, w in zip(outs, want):
             assert np.array_equal(o, w)
     assert_same(want[0], sc.orc.classify(*batches[0], threads=8))
+
+
+def test_launches_survive_cuda_graph_capture_and_replay(torch_cuda):
+    """A poll loop captured once and replayed: sfc_classify and sfc_classify_batches allocate nothing and their
+    ticket slots reset themselves, so a captured sequence can be replayed any number of times."""
+    t = torch_cuda
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    topo = sc.build_chain(8, 2)
+    spec = config3_spec(n_flows=50000, n_ports=topo["n_ports"])
+    install_flows(sc, spec)
+    dp.commit()
+    nb, b = 24, 4096
+    hdr, ports = gen_dev(t, dp, spec, 0, nb * b)
+    want = t.from_numpy(sc.orc.classify(hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), threads=8).view(np.int64).copy()).cuda()
+    res = t.zeros(nb * b, dtype=t.int64, device="cuda")
+    # warm up outside capture (first launches set function attributes)
+    st = t.cuda.current_stream().cuda_stream
+    dp.classify(hdr.data_ptr(), ports.data_ptr(), res.data_ptr(), b, consts.F_OVERLAP, st)
+    dp.classify_batches([(hdr.data_ptr(), ports.data_ptr(), res.data_ptr(), b)], consts.F_OVERLAP, st)
+    t.cuda.synchronize()
+    g = t.cuda.CUDAGraph()
+    with t.cuda.graph(g):
+        s = t.cuda.current_stream().cuda_stream
+        for i in range(nb // 2):  # first half: one launch per batch
+            dp.classify(hdr.data_ptr() + i * b * 64, ports.data_ptr() + i * b * 2, res.data_ptr() + i * b * 8, b, consts.F_OVERLAP, s)
+        rest = [(hdr.data_ptr() + i * b * 64, ports.data_ptr() + i * b * 2, res.data_ptr() + i * b * 8, b) for i in range(nb // 2, nb)]
+        dp.classify_batches(rest, consts.F_OVERLAP, s)  # second half: one launch for all
+    for _ in range(5):
+        res.zero_()
+        g.replay()
+        t.cuda.synchronize()
+        assert t.equal(res, want)
