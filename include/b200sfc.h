@@ -279,6 +279,9 @@ int sfc_table_import_device(sfc_handle* h, const void* dptr, size_t len, void* c
  * are DEVICE pointers on the handle's device.  Asynchronous on `cuda_stream` (a cudaStream_t,
  * NULL = legacy default stream).  One caller thread per stream; threads on different streams may
  * share the handle (up to 256 classify launches in flight per handle).
+ * The call allocates nothing and synchronises nothing, so — after one launch outside capture, which
+ * sets the kernel's attributes — it and sfc_classify_batches may be captured into a CUDA graph and
+ * replayed (tests/test_gpu_parity.py).
  * No reference counterpart — this is the lookup the reference delegates to OVS / FXP hardware. */
 int sfc_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result,
                  size_t n, uint32_t flags, void* cuda_stream);
