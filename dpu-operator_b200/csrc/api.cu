@@ -11,6 +11,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <shared_mutex>
 #include <string>
 #include <vector>
 
@@ -61,7 +63,7 @@ struct sfc_handle {
     unsigned long long* d_counters = nullptr;
     std::atomic<uint64_t> launches{0};  // data-plane threads on different streams share the handle
     EncodeTiledFn encode = nullptr;
-    int ctas_per_sm[24] = {0};  // 0-3 shipped variants, 4-12 tune variants, 16-19 multi-batch variants, 20-21 40-register variants
+    int ctas_per_sm[40] = {0};  // 0-3 shipped variants, 4-15 tune variants (make tune), 16-19 multi-batch variants, 20-21 40-register variants
     bool low_regs = false;      // committed flow tables are too big for L2: use the 40-register variants
     int tune_tile = 0, tune_stages = 0;  // SFC_TUNE=tile,stages (experiments)
     int tune_ctas = 0, tune_carveout = -1;  // cap on resident CTAs per SM / shared-memory carveout percent
@@ -83,17 +85,24 @@ struct sfc_handle {
     uint64_t host_last[kHostBufs] = {};     // number of the chunk last submitted on the slot
     float host_ms_acc = 0.f;
     float last_kernel_ms = -1.f;
-    // host shadows of the committed flow tables + staging for incremental commits
-    FlowTable shadow4, shadow6;
-    std::vector<uint32_t> shadow4_mem, shadow6_mem;
-    ImageHeader header{};  // header of the committed image (host copy)
+    // Host copy of the committed image (host_image below) + views of its flow tables: rule edits are applied
+    // to the copy, every 32-byte sector they change is noted, and a commit ships exactly those sectors.
+    FlowTable shadow4, shadow6;  // format 1 views into host_image
+    IndexedFlows shadow2;        // format 2 view into host_image
+    ImageHeader header{};        // header of the committed image (host copy)
     bool shadow_valid = false;
-    uint8_t* h_patch = nullptr;   // pinned: [indices u32 ...][bucket data ...]
+    uint8_t* h_patch = nullptr;  // pinned: [sector numbers u32 ...][sector data ...]
     uint8_t* d_patch = nullptr;
     size_t patch_cap = 0;
     cudaEvent_t patch_done = nullptr;
+    cudaStream_t cs = nullptr;   // the library's own stream for sfc_commit
     uint64_t n_full_commits = 0, n_incremental_commits = 0, n_patched_buckets = 0;
-    // offline handles (device_ordinal -1): rule staging and image building only, no CUDA calls
+    // `T` is what a launch copies; commits replace it.  Launches hold the lock shared from the copy until the
+    // kernel is enqueued, a commit holds it exclusively while it swaps T — so once a commit has published, every
+    // launch that can still see the old tables is already in a stream, and a device-wide wait retires them.
+    std::shared_mutex tmu;
+    // host copy of the committed image (empty after an import from device memory); for offline handles
+    // (device_ordinal -1: rule staging and image building only, no CUDA calls) this IS the committed image
     std::vector<uint8_t> host_image;
     bool offline() const { return device < 0; }
 };
@@ -159,6 +168,17 @@ void fill_tables(DevTables& T, const ImageHeader& H, const uint8_t* b, unsigned 
     T.flow6_slots = H.flow6_slots;
     T.flow6_nhash = H.flow6_nhash;
     T.flow6_count = H.flow6_count;
+    T.flow_format = H.flow_format;
+    T.fidx = (const uint32_t*)(b + H.fidx_off);
+    T.frec = (const uint32_t*)(b + H.frec_off);
+    T.fidx_nbuckets = H.fidx_nbuckets;
+    T.fidx_bits = H.fidx_bits;
+    expand_seed(H.fidx_seed, T.S2, kFlow6SeedWords);
+    if (H.flow_format == kFlowFormatIndexed && probe_mode < 0) {
+        // index + records of a small rule set live in L1 (configs[1]: 6 KB + 32 KB)
+        const uint64_t bytes = (uint64_t)H.fidx_nbuckets * 32 + (uint64_t)H.frec_used * 32;
+        T.flow4_mode = bytes <= (96u << 10) ? kProbeL1 : 0u;
+    }
     T.l2x = (const L2Entry*)(b + H.l2x_off);
     T.l2x_mask = H.l2x_mask;
     T.l2x_count = H.l2x_count;
@@ -186,45 +206,62 @@ void fill_tables(DevTables& T, const ImageHeader& H, const uint8_t* b, unsigned 
     T.counters = counters;
 }
 
-void bind_tables(sfc_handle* h) {
-    ImageHeader H;
-    cudaMemcpy(&H, h->d_image, sizeof(H), cudaMemcpyDeviceToHost);
-    fill_tables(h->T, H, h->d_image, h->d_counters, h->probe_mode);
+// Which register budget the committed tables want (see launch_classify).
+bool wants_low_regs(const sfc_handle* h, const ImageHeader& H) {
+    // what the probes of one launch range over: flow slots, trie nodes and tail records
+    uint64_t probed = (uint64_t)H.flow4_nbuckets * H.flow4_slots * kFlow4BucketBytes * (H.flow4_count ? 1 : 0) +
+                      (uint64_t)H.flow6_nbuckets * H.flow6_slots * kFlow6BucketBytes * (H.flow6_count ? 1 : 0);
+    if (H.flow_format == kFlowFormatIndexed) probed = (uint64_t)H.fidx_nbuckets * 32 + (uint64_t)H.frec_used * 32;
+    if (H.lpm4_count) probed += (uint64_t)H.lpm4_nnodes * 1024 + (uint64_t)H.lpm4_ntails * sizeof(LpmTail);
+    if (H.lpm6_count) probed += (uint64_t)H.lpm6_nnodes * 1024 + (uint64_t)H.lpm6_ntails * sizeof(LpmTail);
+    // measured (profiles/r01_tuning.md): no difference around 20 MB, 5-10 % in favour of 40 registers from 30 MB up,
+    // 7 % against when the table sits in L1
+    return h->occ_mode < 0 ? probed > (24ull << 20) : h->occ_mode > 0;
+}
+
+// Make `d` (a device copy of an image whose header is H) the committed image: publish the new table
+// descriptor, then wait until every launch that may still read the old image has finished, then free it.
+int publish_image(sfc_handle* h, uint8_t* d, size_t len, const ImageHeader& H) {
+    DevTables T{};
+    fill_tables(T, H, d, h->d_counters, h->probe_mode);
+    uint8_t* old = nullptr;
     {
-        // what the probes of one launch range over: flow slots, trie nodes and tail records
-        uint64_t probed = (uint64_t)H.flow4_nbuckets * H.flow4_slots * kFlow4BucketBytes * (H.flow4_count ? 1 : 0) +
-                          (uint64_t)H.flow6_nbuckets * H.flow6_slots * kFlow6BucketBytes * (H.flow6_count ? 1 : 0);
-        if (H.lpm4_count) probed += (uint64_t)H.lpm4_nnodes * 1024 + (uint64_t)H.lpm4_ntails * sizeof(LpmTail);
-        if (H.lpm6_count) probed += (uint64_t)H.lpm6_nnodes * 1024 + (uint64_t)H.lpm6_ntails * sizeof(LpmTail);
-        // measured (profiles/r01_tuning.md): no difference around 20 MB, 5-10 % in favour of 40 registers from 30 MB up,
-        // 7 % against when the table sits in L1
-        h->low_regs = h->occ_mode < 0 ? probed > (24ull << 20) : h->occ_mode > 0;
+        std::unique_lock<std::shared_mutex> lk(h->tmu);
+        old = h->d_image;
+        h->T = T;
+        h->d_image = d;
+        h->image_bytes = len;
+        h->low_regs = wants_low_regs(h, H);
+        h->epoch = H.epoch;
+        h->flow_first[0] = H.flow_format == kFlowFormatIndexed ? H.fidx_first : H.flow4_first;
+        h->flow_first[1] = H.flow6_first;
     }
-    h->epoch = H.epoch;
-    h->flow_first[0] = H.flow4_first;
-    h->flow_first[1] = H.flow6_first;
+    if (old) {
+        // launches enqueued before the swap may still be reading `old`; none can be enqueued on it any more
+        cudaError_t e = cudaDeviceSynchronize();
+        cudaFree(old);
+        if (e != cudaSuccess) return fail(h, -EIO, "cudaDeviceSynchronize: %s", cudaGetErrorString(e));
+    }
+    return 0;
 }
 
 int install_image_from_host(sfc_handle* h, const uint8_t* img, size_t len) {
     uint8_t* d = nullptr;
     CUDA_TRY(h, cudaMalloc(&d, len));
-    cudaError_t e = cudaMemcpy(d, img, len, cudaMemcpyHostToDevice);
+    cudaError_t e = cudaMemcpy(d, img, len, cudaMemcpyHostToDevice);  // returns when the copy has landed
     if (e != cudaSuccess) {
         cudaFree(d);
         return fail(h, -EIO, "image upload: %s", cudaGetErrorString(e));
     }
-    CUDA_TRY(h, cudaDeviceSynchronize());
-    if (h->d_image) cudaFree(h->d_image);
-    h->d_image = d;
-    h->image_bytes = len;
-    bind_tables(h);
-    return 0;
+    ImageHeader H;
+    memcpy(&H, img, sizeof(H));
+    return publish_image(h, d, len, H);
 }
 
-template <int TILE, int STAGES, bool C, bool A, int OCC = 0>
+template <int TILE, int STAGES, bool C, bool A, int OCC = 0, int FMT = 1>
 int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
                    uint32_t flags, cudaStream_t st) {
-    auto kern = classify_kernel<TILE, STAGES, C, A, false, OCC>;
+    auto kern = classify_kernel<TILE, STAGES, C, A, false, OCC, FMT>;
     constexpr int smem = SmemLayout<TILE, STAGES, A>::kBytes;
     if (!h->ctas_per_sm[slot]) {
         CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -272,10 +309,10 @@ int launch_variant(sfc_handle* h, int slot, const void* hdr, const uint16_t* in_
 
 // One launch over the batches of `L` (already laid out: row0 / tile0 filled in, `rows` = extent of the
 // tensor map in 64-byte records from L.base).
-template <bool C, bool A, int OCC = 0>
+template <bool C, bool A, int OCC = 0, int FMT = 1>
 int launch_multi(sfc_handle* h, int slot, const BatchList& L, uint64_t rows, uint32_t n_tiles, uint32_t flags,
                  cudaStream_t st) {
-    auto kern = classify_kernel<kTile, stages_for<A>(), C, A, true, OCC>;
+    auto kern = classify_kernel<kTile, stages_for<A>(), C, A, true, OCC, FMT>;
     constexpr int smem = SmemLayout<kTile, stages_for<A>(), A>::kBytes;
     if (!h->ctas_per_sm[slot]) {
         CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -314,11 +351,14 @@ int launch_multi(sfc_handle* h, int slot, const BatchList& L, uint64_t rows, uin
 
 int launch_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
                     uint32_t flags, cudaStream_t st) {
-    if (!h->d_image) return fail(h, -EINVAL, "sfc_classify: no committed table image (call sfc_commit)");
     if (((uintptr_t)hdr & 15) != 0) return fail(h, -EINVAL, "sfc_classify: hdr must be 16-byte aligned");
     if (n > (1ull << 31)) return fail(h, -EINVAL, "sfc_classify: at most 2^31 packets per call");
+    // held from the choice of the kernel variant until the launch is in its stream (see sfc_handle::tmu)
+    std::shared_lock<std::shared_mutex> lk(h->tmu);
+    if (!h->d_image) return fail(h, -EINVAL, "sfc_classify: no committed table image (call sfc_commit)");
     bool c = flags & SFC_F_COUNTERS, a = h->T.acl_nrules > 0;
-    if (!c && !a && h->tune_tile) {  // experiment hook: SFC_TUNE=tile,stages
+#ifdef SFC_TUNE_BUILD  // experiment hook (make tune): SFC_TUNE=tile,stages or options tune_tile / tune_stages
+    if (!c && !a && h->tune_tile) {
 #define SFC_TUNE_CASE(slot, T_, S_) \
     if (h->tune_tile == T_ && h->tune_stages == S_) return launch_variant<T_, S_, false, false>(h, slot, hdr, in_port, result, n, flags, st);
         SFC_TUNE_CASE(4, 64, 4)
@@ -330,25 +370,44 @@ int launch_classify(sfc_handle* h, const void* hdr, const uint16_t* in_port, uin
         SFC_TUNE_CASE(10, 512, 2)
         SFC_TUNE_CASE(11, 512, 3)
         SFC_TUNE_CASE(12, 768, 2)
+        SFC_TUNE_CASE(13, 256, 6)
+        SFC_TUNE_CASE(14, 256, 8)
+        SFC_TUNE_CASE(15, 128, 4)
 #undef SFC_TUNE_CASE
     }
-    if (c && a) return launch_variant<kTileAcl, kStagesAcl, true, true>(h, 3, hdr, in_port, result, n, flags, st);
-    if (h->low_regs && !a) {  // probes wait on L2 / DRAM: five CTAs per SM at 40 registers (cfg3: 20.9 vs 22.3 us per Mi)
-        if (c) return launch_variant<kTile, kStages, true, false, 5>(h, 21, hdr, in_port, result, n, flags, st);
-        return launch_variant<kTile, kStages, false, false, 5>(h, 20, hdr, in_port, result, n, flags, st);
+#endif
+    // one compiled kernel per (counters, ACL, register budget, flow table format); slot = index into ctas_per_sm
+    const bool low = h->low_regs && !a;  // probes wait on L2 / DRAM: five CTAs per SM at 40 registers (cfg3: 20.9 vs 22.3 us per Mi)
+#define SFC_GO(slot, C_, A_, OCC_, FMT_)                                                                              \
+    return launch_variant<(A_) ? kTileAcl : kTile, (A_) ? kStagesAcl : kStages, C_, A_, OCC_, FMT_>(h, slot, hdr, in_port, \
+                                                                                                  result, n, flags, st)
+    if (h->T.flow_format == kFlowFormatIndexed) {
+        if (c && a) SFC_GO(27, true, true, 0, 2);
+        if (low && c) SFC_GO(29, true, false, 5, 2);
+        if (low) SFC_GO(28, false, false, 5, 2);
+        if (c) SFC_GO(26, true, false, 0, 2);
+        if (a) SFC_GO(25, false, true, 0, 2);
+        SFC_GO(24, false, false, 0, 2);
     }
-    if (c) return launch_variant<kTile, kStages, true, false>(h, 2, hdr, in_port, result, n, flags, st);
-    if (a) return launch_variant<kTileAcl, kStagesAcl, false, true>(h, 1, hdr, in_port, result, n, flags, st);
-    return launch_variant<kTile, kStages, false, false>(h, 0, hdr, in_port, result, n, flags, st);
+    if (c && a) SFC_GO(3, true, true, 0, 1);
+    if (low && c) SFC_GO(21, true, false, 5, 1);
+    if (low) SFC_GO(20, false, false, 5, 1);
+    if (c) SFC_GO(2, true, false, 0, 1);
+    if (a) SFC_GO(1, false, true, 0, 1);
+    SFC_GO(0, false, false, 0, 1);
+#undef SFC_GO
 }
 
-// Incremental commit: write `n` whole buckets (bucket_words u32 each) into a flow table in place.
-// Runs in stream order between classify launches, never concurrently with one on the same stream.
-__global__ void patch_buckets_kernel(uint32_t* table, const uint32_t* idx, const uint32_t* data, uint32_t n,
-                                     uint32_t bucket_words) {
-    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t b = t / bucket_words, w = t % bucket_words;
-    if (b < n) table[(size_t)idx[b] * bucket_words + w] = data[(size_t)b * bucket_words + w];
+// Incremental commit: write `n` 32-byte sectors into the image in place, one thread per sector and one
+// 32-byte store per thread, so that a lookup running beside it sees each sector either old or new.
+__global__ void patch_sectors_kernel(uint8_t* image, const uint32_t* __restrict__ sector, const uint4* __restrict__ data,
+                                     uint32_t n) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const uint4 a = data[2 * t], b = data[2 * t + 1];
+    asm volatile("st.global.v8.u32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(image + (size_t)sector[t] * 32), "r"(a.x),
+                 "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w)
+                 : "memory");
 }
 
 __global__ void gen_kernel(sfc_gen_spec spec, uint64_t first, uint64_t n, uint8_t* hdr, uint16_t* in_port) {
@@ -399,7 +458,9 @@ int sfc_create(int device_ordinal, sfc_handle** out) {
         return -ENOSYS;
     }
     h->encode = (EncodeTiledFn)fn;
+#ifdef SFC_TUNE_BUILD
     if (const char* tune = getenv("SFC_TUNE")) sscanf(tune, "%d,%d", &h->tune_tile, &h->tune_stages);
+#endif
     if (cudaMalloc(&h->d_counters, SFC_CNT_TOTAL * sizeof(uint64_t)) != cudaSuccess ||
         cudaMemset(h->d_counters, 0, SFC_CNT_TOTAL * sizeof(uint64_t)) != cudaSuccess ||
         cudaMalloc(&h->d_tickets, kTicketRing * kTicketStride * sizeof(uint32_t)) != cudaSuccess ||
@@ -425,6 +486,7 @@ int sfc_destroy(sfc_handle* h) {
     if (h->h_patch) cudaFreeHost(h->h_patch);
     if (h->d_patch) cudaFree(h->d_patch);
     if (h->patch_done) cudaEventDestroy(h->patch_done);
+    if (h->cs) cudaStreamDestroy(h->cs);
     for (int i = 0; i < kHostBufs; ++i) {
         if (h->d_hdr[i]) cudaFree(h->d_hdr[i]);
         if (h->d_port[i]) cudaFree(h->d_port[i]);
@@ -442,7 +504,7 @@ const char* sfc_last_error(const sfc_handle* h) { return h ? h->err.c_str() : "n
 int sfc_set_option(sfc_handle* h, const char* name, long value) {
     if (!h || !name) return -EINVAL;
     if (!strcmp(name, "flow_load_pct")) {
-        if (value < 5 || value > 90) return fail(h, -EINVAL, "flow_load_pct must be 5..90");
+        if (value != 0 && (value < 5 || value > 90)) return fail(h, -EINVAL, "flow_load_pct must be 0 (the format's default) or 5..90");
         h->rs.other_dirty = true;
         h->rs.flow_load_pct = (int)value;
         return 0;
@@ -484,9 +546,17 @@ int sfc_set_option(sfc_handle* h, const char* name, long value) {
     if (!strcmp(name, "flow_probe_mode")) {  // -1 auto, bit0 eager dual probe, bit1 probes may live in L1
         if (value < -1 || value > 3) return fail(h, -EINVAL, "flow_probe_mode must be -1..3");
         h->probe_mode = (int)value;
+        std::unique_lock<std::shared_mutex> lk(h->tmu);
         if (h->d_image) h->T.flow4_mode = value >= 0 ? (uint32_t)value : h->T.flow4_mode;
         return 0;
     }
+    if (!strcmp(name, "flow_format")) {  // 0 by size, 1 one-sector cuckoo tables per family, 2 fingerprint index + records
+        if (value < 0 || value > 2) return fail(h, -EINVAL, "flow_format must be 0, 1 or 2");
+        h->rs.other_dirty = true;
+        h->rs.flow_format = (int)value;
+        return 0;
+    }
+#ifdef SFC_TUNE_BUILD
     if (!strcmp(name, "tune_tile")) {  // experiment hooks: pick a compiled (tile, stages) variant
         h->tune_tile = (int)value;
         return 0;
@@ -500,6 +570,7 @@ int sfc_set_option(sfc_handle* h, const char* name, long value) {
         for (int& c : h->ctas_per_sm) c = 0;  // re-derive occupancy on the next launch
         return 0;
     }
+#endif
     return fail(h, -ENOENT, "unknown option '%s'", name);
 }
 
@@ -557,7 +628,7 @@ long sfc_port_list(const sfc_handle* h, char* buf, size_t len) {
 // =================================================================== L2 steering =========
 int sfc_l2_rule_add(sfc_handle* h, uint16_t in_port, uint16_t out_port, const uint8_t* dst_mac, uint32_t* rule_id) {
     if (!h) return -EINVAL;
-    h->rs.other_dirty = true;  // not a flow edit: the next commit rebuilds the image
+    h->rs.l2_dirty = true;  // the next commit rebuilds the idle copy of the L2 tables, not the image
     if (in_port >= SFC_MAX_PORTS || out_port >= SFC_MAX_PORTS)
         return fail(h, -EINVAL, "sfc_l2_rule_add: port id out of range");
     L2Rule r{};
@@ -583,7 +654,7 @@ int sfc_l2_rule_add(sfc_handle* h, uint16_t in_port, uint16_t out_port, const ui
 
 int sfc_l2_rule_del(sfc_handle* h, uint16_t in_port, const uint8_t* dst_mac) {
     if (!h) return -EINVAL;
-    h->rs.other_dirty = true;  // not a flow edit: the next commit rebuilds the image
+    h->rs.l2_dirty = true;  // the next commit rebuilds the idle copy of the L2 tables, not the image
     auto& v = h->rs.l2;
     v.erase(std::remove_if(v.begin(), v.end(),
                            [&](const L2Rule& e) {
@@ -754,23 +825,38 @@ int sfc_clear(sfc_handle* h) {
 
 namespace {
 
-// Point the host shadows at a freshly built image (kept in shadowN_mem) so later flow edits can be
-// applied to single buckets.
-void adopt_shadows(sfc_handle* h, const std::vector<uint8_t>& img) {
-    memcpy(&h->header, img.data(), sizeof(ImageHeader));
+// Point the shadow views at the host copy of the committed image so that later edits can be applied
+// sector by sector.
+void adopt_shadows(sfc_handle* h) {
+    uint8_t* base = h->host_image.data();
+    memcpy(&h->header, base, sizeof(ImageHeader));
     const ImageHeader& H = h->header;
-    auto take = [&](FlowTable& t, std::vector<uint32_t>& mem, bool v6, uint64_t off, uint32_t nb, uint32_t slots, uint32_t nhash, uint64_t seed) {
+    auto take = [&](FlowTable& t, bool v6, uint64_t off, uint32_t nb, uint32_t slots, uint32_t nhash, uint64_t seed) {
         t = FlowTable();
         t.v6 = v6;
-        mem.assign((const uint32_t*)(img.data() + off), (const uint32_t*)(img.data() + off) + (size_t)nb * slots * t.words());
-        t.tab = mem.data();
+        t.tab = (uint32_t*)(base + off);
         t.nbuckets = nb;
         t.slots = (int)slots;
         t.nhash = (int)nhash;
         expand_seed(seed, t.S, v6 ? kFlow6SeedWords : kFlow4SeedWords);
     };
-    take(h->shadow4, h->shadow4_mem, false, H.flow4_off, H.flow4_nbuckets, H.flow4_slots, H.flow4_nhash, H.flow4_seed);
-    take(h->shadow6, h->shadow6_mem, true, H.flow6_off, H.flow6_nbuckets, H.flow6_slots, H.flow6_nhash, H.flow6_seed);
+    take(h->shadow4, false, H.flow4_off, H.flow4_nbuckets, H.flow4_slots, H.flow4_nhash, H.flow4_seed);
+    take(h->shadow6, true, H.flow6_off, H.flow6_nbuckets, H.flow6_slots, H.flow6_nhash, H.flow6_seed);
+    IndexedFlows& x = h->shadow2;
+    x = IndexedFlows();
+    if (H.flow_format == kFlowFormatIndexed) {
+        x.idx = (uint32_t*)(base + H.fidx_off);
+        x.rec = (uint32_t*)(base + H.frec_off);
+        x.nbuckets = H.fidx_nbuckets;
+        x.bits = H.fidx_bits;
+        x.units = H.frec_units;
+        x.used = H.frec_used;
+        x.idx_sector0 = (uint32_t)(H.fidx_off / 32);
+        x.rec_sector0 = (uint32_t)(H.frec_off / 32);
+        x.count = H.flow4_count + H.flow6_count;
+        x.second = x.count - H.fidx_first;
+        expand_seed(H.fidx_seed, x.S, kFlow6SeedWords);
+    }
     h->shadow_valid = true;
 }
 
@@ -778,106 +864,143 @@ int full_commit(sfc_handle* h) {
     std::vector<uint8_t> img;
     std::string err;
     if (!build_image(h->rs, h->epoch + 1, img, err)) return fail(h, -ENOSPC, "sfc_commit: %s", err.c_str());
-    adopt_shadows(h, img);
+    if (!h->offline()) {
+        // the device first: if this fails the old image, its host copy and the edit log all stay as they were
+        int rc = install_image_from_host(h, img.data(), img.size());
+        if (rc) return rc;
+    } else {
+        h->image_bytes = img.size();
+        ++h->epoch;
+    }
+    h->host_image.swap(img);
+    adopt_shadows(h);
     h->rs.flow_log.clear();
+    h->rs.l2_dirty = false;
     h->rs.other_dirty = false;
     ++h->n_full_commits;
-    if (h->offline()) {
-        h->host_image.swap(img);
-        h->image_bytes = h->host_image.size();
-        ++h->epoch;
-        return 0;
-    }
-    return install_image_from_host(h, img.data(), img.size());
+    return 0;
 }
 
-// Apply the logged flow edits to the shadows and ship only the buckets they touched.
-// Returns 1 if done, 0 if a full rebuild is needed (nothing has been changed on the device then), < 0 on error.
+// Apply the logged flow edits and a changed L2 rule set to the host copy of the image and ship only the
+// sectors they changed.  Returns 1 if done, 0 if a full rebuild is needed, < 0 on error.
+// Whenever 0 or an error is returned after the host copy was touched, shadow_valid is false: the next commit
+// rebuilds from the rule store (the source of truth), so no edit is ever applied twice.
 int incremental_commit(sfc_handle* h, cudaStream_t st, bool async) {
     RuleStore& rs = h->rs;
-    if (rs.other_dirty || !h->shadow_valid || (!h->offline() && !h->d_image)) return 0;
-    auto room = [&](const FlowTable& t) {  // flows the table may hold before it has to be rebuilt larger
-        const long max_load = t.slots == 2 ? 85 : (rs.flow_hashes == 2 ? 45 : 85);
-        return (long)t.nbuckets * t.slots * max_load / 100;
+    if (rs.other_dirty || !h->shadow_valid || h->host_image.empty() || (!h->offline() && !h->d_image)) return 0;
+    ImageHeader& H = h->header;
+    const bool indexed = H.flow_format == kFlowFormatIndexed;
+    long c4 = H.flow4_count, c6 = H.flow6_count, adds = 0;
+    for (auto& ch : rs.flow_log) {
+        (ch.rec.ip_ver == 6 ? c6 : c4) += ch.add ? 1 : -1;
+        adds += ch.add;
+    }
+    if (indexed) {
+        if (adds > h->shadow2.room()) return 0;
+    } else {
+        auto room = [&](const FlowTable& t) {  // flows the table may hold before it has to be rebuilt larger
+            const long max_load = t.slots == 2 ? 85 : (rs.flow_hashes == 2 ? 45 : 85);
+            return (long)t.nbuckets * t.slots * max_load / 100;
+        };
+        if (c4 > room(h->shadow4) || c6 > room(h->shadow6)) return 0;
+    }
+    std::vector<uint32_t> dirty;  // image sector numbers
+    auto bail = [&](int rc) {
+        h->shadow_valid = false;
+        return rc;
     };
-    long c4 = h->header.flow4_count, c6 = h->header.flow6_count;
-    for (auto& ch : rs.flow_log) (ch.rec.ip_ver == 6 ? c6 : c4) += ch.add ? 1 : -1;
-    if (c4 > room(h->shadow4) || c6 > room(h->shadow6)) return 0;
-    std::vector<uint32_t> dirty4, dirty6;
-    // A failed insertion walk leaves the shadow with one flow homeless: fall back to a rebuild, which
-    // re-adopts the shadows from the rule store (the source of truth).  Nothing has reached the device yet.
+    // ---- flows ----
     uint32_t rec[kFlow6BucketWords];
+    std::vector<uint32_t> slots;
     for (auto& ch : rs.flow_log) {
         const FlowRec& f = ch.rec;
-        FlowTable& t = f.ip_ver == 6 ? h->shadow6 : h->shadow4;
-        std::vector<uint32_t>& dirty = f.ip_ver == 6 ? dirty6 : dirty4;
-        FlowTable::encode(f, f.action == SFC_ACT_FORWARD ? nf_of_port(rs, f.out_port) : (uint32_t)SFC_NF_NONE, rec);
-        bool ok = ch.add ? t.insert(rec, &dirty) : t.erase(rec, &dirty);
-        if (!ok) {
-            h->shadow_valid = false;  // shadow no longer mirrors the device; the rebuild restores it
-            return 0;
+        const uint32_t nf = f.action == SFC_ACT_FORWARD ? nf_of_port(rs, f.out_port) : (uint32_t)SFC_NF_NONE;
+        bool ok;
+        if (indexed) {
+            ok = ch.add ? h->shadow2.insert(f, nf, &dirty) : h->shadow2.erase(f, &dirty);
+        } else {
+            const bool six = f.ip_ver == 6;
+            FlowTable& t = six ? h->shadow6 : h->shadow4;
+            FlowTable::encode(f, nf, rec);
+            slots.clear();
+            ok = ch.add ? t.insert(rec, &slots) : t.erase(rec, &slots);
+            const uint64_t off = six ? H.flow6_off : H.flow4_off;
+            for (uint32_t sl : slots) {  // an IPv4 slot is one sector, an IPv6 slot two
+                const uint32_t s0 = (uint32_t)(off / 32) + sl * (six ? 2u : 1u);
+                dirty.push_back(s0);
+                if (six) dirty.push_back(s0 + 1);
+            }
         }
+        // A failed insertion walk leaves one flow homeless: fall back to a rebuild from the rule store.
+        // Nothing has reached the device yet.
+        if (!ok) return bail(0);
     }
-    auto uniq = [](std::vector<uint32_t>& v) {
-        std::sort(v.begin(), v.end());
-        v.erase(std::unique(v.begin(), v.end()), v.end());
-    };
-    uniq(dirty4);
-    uniq(dirty6);
-    h->header.flow4_count = (uint32_t)c4;
-    h->header.flow6_count = (uint32_t)c6;
-    h->header.epoch = h->epoch + 1;
-    if (h->offline()) {
-        for (uint32_t b : dirty4)
-            memcpy(h->host_image.data() + h->header.flow4_off + (size_t)b * kFlow4BucketBytes, h->shadow4.tab + (size_t)b * kFlow4BucketWords, kFlow4BucketBytes);
-        for (uint32_t b : dirty6)
-            memcpy(h->host_image.data() + h->header.flow6_off + (size_t)b * kFlow6BucketBytes, h->shadow6.tab + (size_t)b * kFlow6BucketWords, kFlow6BucketBytes);
-        memcpy(h->host_image.data(), &h->header, sizeof(ImageHeader));
-    } else {
-        // staging layout: [idx4][idx6][data4][data6][header]
-        size_t n4 = dirty4.size(), n6 = dirty6.size();
-        size_t need = (n4 + n6) * 4 + n4 * kFlow4BucketBytes + n6 * kFlow6BucketBytes + sizeof(ImageHeader) + 64;
-        if (!h->patch_done) CUDA_TRY(h, cudaEventCreateWithFlags(&h->patch_done, cudaEventDisableTiming));
-        else CUDA_TRY(h, cudaEventSynchronize(h->patch_done));  // the previous patch has left the staging buffer
+    H.flow4_count = (uint32_t)c4;
+    H.flow6_count = (uint32_t)c6;
+    if (indexed) {
+        H.frec_used = h->shadow2.used;
+        H.fidx_first = h->shadow2.count - h->shadow2.second;
+    }
+    H.epoch = h->epoch + 1;
+    memcpy(h->host_image.data(), &H, sizeof(ImageHeader));
+    // ---- L2 steering: rebuilt into the idle copy, which becomes the active one ----
+    if (rs.l2_dirty) {
+        if (!h->offline() && !async) {
+            // the idle copy was the active one before the previous commit: launches from back then must be gone
+            cudaError_t e = cudaDeviceSynchronize();
+            if (e != cudaSuccess) return bail(fail(h, -EIO, "cudaDeviceSynchronize: %s", cudaGetErrorString(e)));
+        }
+        if (!rebuild_l2_copy(rs, h->host_image.data(), 1 - (int)H.l2_active, &dirty)) return bail(0);
+        memcpy(&H, h->host_image.data(), sizeof(ImageHeader));
+    }
+    for (uint32_t sct = 0; sct < kImageHeaderBytes / 32; ++sct) dirty.push_back(sct);
+    std::sort(dirty.begin(), dirty.end());
+    dirty.erase(std::unique(dirty.begin(), dirty.end()), dirty.end());
+    if (!h->offline()) {
+        // staging layout: [sector numbers][pad to 32][sector data]
+        const size_t n = dirty.size(), o_data = (n * 4 + 31) & ~(size_t)31, need = o_data + n * 32;
+        auto cuda_bail = [&](cudaError_t e, const char* what) { return bail(fail(h, -EIO, "%s: %s", what, cudaGetErrorString(e))); };
+        cudaError_t e;
+        if (!h->patch_done) {
+            if ((e = cudaEventCreateWithFlags(&h->patch_done, cudaEventDisableTiming)) != cudaSuccess) return cuda_bail(e, "cudaEventCreate");
+        } else if ((e = cudaEventSynchronize(h->patch_done)) != cudaSuccess) {  // the previous patch has left the staging buffer
+            return cuda_bail(e, "cudaEventSynchronize");
+        }
+        if (!async && !h->cs && (e = cudaStreamCreateWithFlags(&h->cs, cudaStreamNonBlocking)) != cudaSuccess) return cuda_bail(e, "cudaStreamCreate");
+        if (!async) st = h->cs;
         if (need > h->patch_cap) {
             if (h->h_patch) cudaFreeHost(h->h_patch);
             if (h->d_patch) cudaFree(h->d_patch);
-            h->patch_cap = std::max<size_t>(need * 2, 1 << 20);
-            CUDA_TRY(h, cudaMallocHost(&h->h_patch, h->patch_cap));
-            CUDA_TRY(h, cudaMalloc(&h->d_patch, h->patch_cap));
+            h->h_patch = h->d_patch = nullptr;
+            h->patch_cap = 0;
+            const size_t cap = std::max<size_t>(need * 2, 1 << 20);
+            if ((e = cudaMallocHost(&h->h_patch, cap)) != cudaSuccess) return cuda_bail(e, "cudaMallocHost");
+            if ((e = cudaMalloc(&h->d_patch, cap)) != cudaSuccess) return cuda_bail(e, "cudaMalloc");
+            h->patch_cap = cap;
         }
         uint8_t* p = h->h_patch;
-        size_t o_idx4 = 0, o_idx6 = n4 * 4, o_d4 = (n4 + n6) * 4, o_d6 = o_d4 + n4 * kFlow4BucketBytes,
-               o_hdr = (o_d6 + n6 * kFlow6BucketBytes + 15) & ~(size_t)15;
-        if (n4) memcpy(p + o_idx4, dirty4.data(), n4 * 4);
-        if (n6) memcpy(p + o_idx6, dirty6.data(), n6 * 4);
-        for (size_t i = 0; i < n4; ++i) memcpy(p + o_d4 + i * kFlow4BucketBytes, h->shadow4.tab + (size_t)dirty4[i] * kFlow4BucketWords, kFlow4BucketBytes);
-        for (size_t i = 0; i < n6; ++i) memcpy(p + o_d6 + i * kFlow6BucketBytes, h->shadow6.tab + (size_t)dirty6[i] * kFlow6BucketWords, kFlow6BucketBytes);
-        memcpy(p + o_hdr, &h->header, sizeof(ImageHeader));
-        CUDA_TRY(h, cudaMemcpyAsync(h->d_patch, p, o_hdr + sizeof(ImageHeader), cudaMemcpyHostToDevice, st));
-        if (n4) {
-            unsigned threads = (unsigned)(n4 * kFlow4BucketWords);
-            patch_buckets_kernel<<<(threads + 255) / 256, 256, 0, st>>>((uint32_t*)(h->d_image + h->header.flow4_off), (const uint32_t*)(h->d_patch + o_idx4),
-                                                                       (const uint32_t*)(h->d_patch + o_d4), (uint32_t)n4, kFlow4BucketWords);
-            ++h->launches;
-        }
-        if (n6) {
-            unsigned threads = (unsigned)(n6 * kFlow6BucketWords);
-            patch_buckets_kernel<<<(threads + 255) / 256, 256, 0, st>>>((uint32_t*)(h->d_image + h->header.flow6_off), (const uint32_t*)(h->d_patch + o_idx6),
-                                                                       (const uint32_t*)(h->d_patch + o_d6), (uint32_t)n6, kFlow6BucketWords);
-            ++h->launches;
-        }
-        CUDA_TRY(h, cudaGetLastError());
-        CUDA_TRY(h, cudaMemcpyAsync(h->d_image, h->d_patch + o_hdr, sizeof(ImageHeader), cudaMemcpyDeviceToDevice, st));
-        CUDA_TRY(h, cudaEventRecord(h->patch_done, st));
-        if (!async) CUDA_TRY(h, cudaStreamSynchronize(st));
-        h->T.flow4_count = (uint32_t)c4;  // the kernel takes its table descriptor by value at launch
-        h->T.flow6_count = (uint32_t)c6;
+        memcpy(p, dirty.data(), n * 4);
+        for (size_t i = 0; i < n; ++i) memcpy(p + o_data + i * 32, h->host_image.data() + (size_t)dirty[i] * 32, 32);
+        if ((e = cudaMemcpyAsync(h->d_patch, p, need, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_bail(e, "cudaMemcpyAsync");
+        patch_sectors_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(h->d_image, (const uint32_t*)h->d_patch,
+                                                                           (const uint4*)(h->d_patch + o_data), (uint32_t)n);
+        ++h->launches;
+        if ((e = cudaGetLastError()) != cudaSuccess) return cuda_bail(e, "patch kernel");
+        if ((e = cudaEventRecord(h->patch_done, st)) != cudaSuccess) return cuda_bail(e, "cudaEventRecord");
+        // sfc_commit: the sectors have landed before the new descriptor is published, so launches on ANY stream
+        // see a finished table.  sfc_commit_stream: published at once; launches on `st` are ordered behind the patch.
+        if (!async && (e = cudaStreamSynchronize(st)) != cudaSuccess) return cuda_bail(e, "cudaStreamSynchronize");
+        DevTables T{};
+        fill_tables(T, H, h->d_image, h->d_counters, h->probe_mode);
+        std::unique_lock<std::shared_mutex> lk(h->tmu);
+        h->T = T;
+        h->flow_first[0] = indexed ? H.fidx_first : H.flow4_first;
     }
     ++h->epoch;
-    h->n_patched_buckets += dirty4.size() + dirty6.size();
+    h->n_patched_buckets += dirty.size() - kImageHeaderBytes / 32;
     ++h->n_incremental_commits;
     rs.flow_log.clear();
+    rs.l2_dirty = false;
     return 1;
 }
 
@@ -944,6 +1067,7 @@ int sfc_table_import(sfc_handle* h, const void* buf, size_t len) {
         h->epoch = H.epoch;
         return 0;
     }
+    h->host_image.clear();
     DeviceGuard g(h->device);
     return install_image_from_host(h, (const uint8_t*)buf, len);
 }
@@ -975,18 +1099,15 @@ int sfc_table_import_device(sfc_handle* h, const void* dptr, size_t len, void* c
     uint8_t* d = nullptr;
     CUDA_TRY(h, cudaMalloc(&d, len));
     cudaError_t e = cudaMemcpyAsync(d, dptr, len, cudaMemcpyDeviceToDevice, st);
-    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) {
         cudaFree(d);
         return fail(h, -EIO, "sfc_table_import_device: %s", cudaGetErrorString(e));
     }
-    if (h->d_image) cudaFree(h->d_image);
-    h->d_image = d;
-    h->image_bytes = len;
     h->shadow_valid = false;
+    h->host_image.clear();
     h->rs.other_dirty = true;
-    bind_tables(h);
-    return 0;
+    return publish_image(h, d, len, H);
 }
 
 // =================================================================== data plane ==========
@@ -1006,7 +1127,6 @@ int sfc_classify_batches(sfc_handle* h, const sfc_batch* batches, uint32_t n_bat
     if (h->offline()) return fail(h, -ENODEV, "offline handle: no device (there is no CPU data path)");
     if (n_batches == 0) return 0;
     if (!batches) return fail(h, -EINVAL, "sfc_classify_batches: null batch list");
-    if (!h->d_image) return fail(h, -EINVAL, "sfc_classify_batches: no committed table image (call sfc_commit)");
     // validate everything before the first launch: a bad descriptor must not leave half the list done
     for (uint32_t i = 0; i < n_batches; ++i) {
         const sfc_batch& b = batches[i];
@@ -1016,6 +1136,8 @@ int sfc_classify_batches(sfc_handle* h, const sfc_batch* batches, uint32_t n_bat
         if (b.n > (1u << 30)) return fail(h, -EINVAL, "sfc_classify_batches: batch %u has more than 2^30 packets", i);
     }
     DeviceGuard g(h->device);
+    std::shared_lock<std::shared_mutex> lk(h->tmu);  // see sfc_handle::tmu
+    if (!h->d_image) return fail(h, -EINVAL, "sfc_classify_batches: no committed table image (call sfc_commit)");
     const bool c = flags & SFC_F_COUNTERS, a = h->T.acl_nrules > 0;
     // Greedy split into launches: at most kMaxBatches descriptors, 2^31 tiles and 2^31 rows of span each
     // (TMA coordinates are signed 32-bit).
@@ -1051,11 +1173,19 @@ int sfc_classify_batches(sfc_handle* h, const sfc_batch* batches, uint32_t n_bat
         for (uint32_t k = 0; k < L.count; ++k) L.b[k].row0 = (uint32_t)((batch_hdr[k] - lo) / 64);
         const uint64_t rows = (hi - lo) / 64;
         int rc;
-        if (h->low_regs && !a && !c) rc = launch_multi<false, false, 5>(h, 22, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
-        else if (c && a) rc = launch_multi<true, true>(h, 19, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
-        else if (c) rc = launch_multi<true, false>(h, 18, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
-        else if (a) rc = launch_multi<false, true>(h, 17, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
-        else rc = launch_multi<false, false>(h, 16, L, rows, (uint32_t)tiles, flags, (cudaStream_t)cuda_stream);
+        const uint32_t nt = (uint32_t)tiles;
+        cudaStream_t s = (cudaStream_t)cuda_stream;
+        if (h->T.flow_format == kFlowFormatIndexed) {
+            if (h->low_regs && !a && !c) rc = launch_multi<false, false, 5, 2>(h, 36, L, rows, nt, flags, s);
+            else if (c && a) rc = launch_multi<true, true, 0, 2>(h, 35, L, rows, nt, flags, s);
+            else if (c) rc = launch_multi<true, false, 0, 2>(h, 34, L, rows, nt, flags, s);
+            else if (a) rc = launch_multi<false, true, 0, 2>(h, 33, L, rows, nt, flags, s);
+            else rc = launch_multi<false, false, 0, 2>(h, 32, L, rows, nt, flags, s);
+        } else if (h->low_regs && !a && !c) rc = launch_multi<false, false, 5>(h, 22, L, rows, nt, flags, s);
+        else if (c && a) rc = launch_multi<true, true>(h, 19, L, rows, nt, flags, s);
+        else if (c) rc = launch_multi<true, false>(h, 18, L, rows, nt, flags, s);
+        else if (a) rc = launch_multi<false, true>(h, 17, L, rows, nt, flags, s);
+        else rc = launch_multi<false, false>(h, 16, L, rows, nt, flags, s);
         if (rc) return rc;
     }
     return 0;
@@ -1184,7 +1314,7 @@ struct StaticDev {
     bool ready = false;
     unsigned char* area = nullptr;  // device address of g_static_area ON THIS DEVICE
     int sm_count = 0;
-    int ctas_per_sm[2] = {0, 0};    // [no ACL, ACL]
+    int ctas_per_sm[4] = {0, 0, 0, 0};  // [no ACL, ACL] x [sector flow tables, indexed flow table]
     EncodeTiledFn encode = nullptr;
     bool resident = false;          // an image was copied in by an earlier call
     ImageHeader header;
@@ -1219,13 +1349,16 @@ int static_setup(int device, StaticDev& d, char* errbuf, size_t errlen) {
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn)
         return static_fail(errbuf, errlen, -ENOSYS, "driver lacks cuTensorMapEncodeTiled");
     d.encode = (EncodeTiledFn)fn;
-    const void* kerns[2] = {(const void*)classify_kernel<kTile, kStages, false, false>,
-                            (const void*)classify_kernel<kTile, kStagesAcl, false, true>};
-    const int smem[2] = {SmemLayout<kTile, kStages, false>::kBytes, SmemLayout<kTile, kStagesAcl, true>::kBytes};
-    for (int v = 0; v < 2; ++v) {
-        e = cudaFuncSetAttribute(kerns[v], cudaFuncAttributeMaxDynamicSharedMemorySize, smem[v]);
+    const void* kerns[4] = {(const void*)classify_kernel<kTile, kStages, false, false, false, 0, 1>,
+                            (const void*)classify_kernel<kTileAcl, kStagesAcl, false, true, false, 0, 1>,
+                            (const void*)classify_kernel<kTile, kStages, false, false, false, 0, 2>,
+                            (const void*)classify_kernel<kTileAcl, kStagesAcl, false, true, false, 0, 2>};
+    const int smem[2] = {SmemLayout<kTile, kStages, false>::kBytes, SmemLayout<kTileAcl, kStagesAcl, true>::kBytes};
+    const int threads[2] = {kTile + 32, kTileAcl + 32};
+    for (int v = 0; v < 4; ++v) {
+        e = cudaFuncSetAttribute(kerns[v], cudaFuncAttributeMaxDynamicSharedMemorySize, smem[v & 1]);
         if (e == cudaSuccess)
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.ctas_per_sm[v], kerns[v], kTile + 32, smem[v]);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.ctas_per_sm[v], kerns[v], threads[v & 1], smem[v & 1]);
         if (e != cudaSuccess || d.ctas_per_sm[v] < 1)
             return static_fail(errbuf, errlen, -EIO, "classify kernel set-up: %s", cudaGetErrorString(e));
     }
@@ -1283,22 +1416,26 @@ extern "C" int sfc_classify_static(int device, const void* image_host, size_t im
     CUtensorMap map;
     cuuint64_t dims[2] = {16, (cuuint64_t)n};
     cuuint64_t strides[1] = {64};
-    cuuint32_t box[2] = {16, (cuuint32_t)(kTile < 256 ? kTile : 256)};
+    cuuint32_t box[2] = {16, (cuuint32_t)256};  // kTile and kTileAcl are multiples of 256 rows
     cuuint32_t estr[2] = {1, 1};
     CUresult r = d.encode(&map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(hdr), dims, strides, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return static_fail(errbuf, errlen, -EIO, "cuTensorMapEncodeTiled failed (%d)", (int)r);
-    const bool acl = T.acl_nrules > 0;
-    const uint64_t n_tiles = (n + kTile - 1) / kTile;
-    const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)d.sm_count * d.ctas_per_sm[acl ? 1 : 0]);
+    const bool acl = T.acl_nrules > 0, indexed = T.flow_format == kFlowFormatIndexed;
+    const int tile = acl ? kTileAcl : kTile;
+    const uint64_t n_tiles = (n + tile - 1) / tile;
+    const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)d.sm_count * d.ctas_per_sm[(acl ? 1 : 0) + (indexed ? 2 : 0)]);
     uint32_t* ticket = (uint32_t*)d.area;  // {draw counter, finished producers}: cleared above, reset by the kernel too
-    if (acl)
-        classify_kernel<kTile, kStagesAcl, false, true><<<grid, kTile + 32, SmemLayout<kTile, kStagesAcl, true>::kBytes, st>>>(
-            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, 0u, T, NoBatches{});
-    else
-        classify_kernel<kTile, kStages, false, false><<<grid, kTile + 32, SmemLayout<kTile, kStages, false>::kBytes, st>>>(
-            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, 0u, T, NoBatches{});
+#define SFC_STATIC_GO(A_, FMT_)                                                                                          \
+    classify_kernel<(A_) ? kTileAcl : kTile, (A_) ? kStagesAcl : kStages, false, A_, false, 0, FMT_>                      \
+        <<<grid, ((A_) ? kTileAcl : kTile) + 32, SmemLayout<(A_) ? kTileAcl : kTile, (A_) ? kStagesAcl : kStages, A_>::kBytes, st>>>( \
+            map, in_port, result, (uint32_t)n, (uint32_t)n_tiles, ticket, 0u, T, NoBatches{})
+    if (acl && indexed) SFC_STATIC_GO(true, 2);
+    else if (acl) SFC_STATIC_GO(true, 1);
+    else if (indexed) SFC_STATIC_GO(false, 2);
+    else SFC_STATIC_GO(false, 1);
+#undef SFC_STATIC_GO
     e = cudaGetLastError();
     if (e != cudaSuccess) return static_fail(errbuf, errlen, -EIO, "kernel launch: %s", cudaGetErrorString(e));
     return 0;

@@ -27,6 +27,11 @@ struct DevTables {
     uint32_t flow6_nbuckets, flow6_nhash, flow6_count;
     uint32_t S4[kFlow4SeedWords];
     uint32_t S6[kFlow6SeedWords];
+    // format 2 (indexed): one fingerprint index + dense record units for both families
+    const uint32_t* fidx;
+    const uint32_t* frec;
+    uint32_t flow_format, fidx_nbuckets, fidx_bits;
+    uint32_t S2[kFlow6SeedWords];
     const L2Entry* l2x;
     uint32_t l2x_mask, l2x_count;
     const L2Wild* l2w;
@@ -346,6 +351,79 @@ __device__ __forceinline__ bool flow6_lookup(const DevTables& T, const Key& k, u
     return hit;
 }
 
+
+// ---- format 2: fingerprint index, then one record (sfc_common.h) ----
+// One code path for IPv4 and IPv6: the index probe does not know the family, an IPv6 record is one more
+// sector.  A bucket is one sector: seven entries and the count of flows that overflowed into their second
+// bucket, so a miss that finds that count at zero stops after one load.
+__device__ __forceinline__ bool flow2_probe_unit(const DevTables& T, uint32_t unit, const Key& k, uint32_t tag, bool v6,
+                                                 const uint32_t* c, uint32_t& rhi, uint32_t& rlo) {
+    const uint32_t* p = T.frec + (size_t)unit * kFrecUnitWords;
+    uint32_t u[8], v[8];
+    if (T.flow4_mode & kProbeL1) ldg256_l1(p, u); else ldg256(p, u);
+    bool eq = u[0] == tag && u[1] == k.ports && u[4] == c[0] && u[5] == c[1] && u[6] == c[2] && u[7] == c[3];
+    if (v6) {  // uniform code up to here; the second unit only for IPv6 lanes
+        if (T.flow4_mode & kProbeL1) ldg256_l1(p + 8, v); else ldg256(p + 8, v);
+        eq = eq && v[0] == k.dip[0] && v[1] == k.dip[1] && v[2] == k.dip[2] && v[3] == k.dip[3];
+    }
+    rhi = u[2];
+    rlo = u[3];
+    return eq;
+}
+__device__ __forceinline__ bool flow2_probe_bucket(const DevTables& T, uint32_t b, uint32_t fpw, uint32_t mask, const Key& k,
+                                                   uint32_t tag, bool v6, const uint32_t* c, uint32_t& rhi, uint32_t& rlo,
+                                                   uint32_t& overflow) {
+    uint32_t e[8];
+    const uint32_t* p = T.fidx + (size_t)b * kFidxBucketWords;
+    if (T.flow4_mode & kProbeL1) ldg256_l1(p, e); else ldg256(p, e);
+    overflow = e[7];
+    // first entry carrying our fingerprint, and how many do (more than one is rare: 7 / 2^(32 - bits))
+    uint32_t cand = 0, ncand = 0;
+#pragma unroll
+    for (int i = 0; i < kFidxEntries; ++i) {
+        const uint32_t d = e[i] ^ fpw;  // equal fingerprints leave unit + 1 (1 .. mask); an empty entry never passes
+        const bool ok = d - 1u < mask;
+        cand = (ok && !cand) ? d : cand;
+        ncand += ok;
+    }
+    if (!cand) return false;
+    if (flow2_probe_unit(T, cand - 1u, k, tag, v6, c, rhi, rlo)) return true;
+    if (ncand > 1) {
+        bool skipped = false;
+#pragma unroll 1
+        for (int i = 0; i < kFidxEntries; ++i) {
+            uint32_t ei = 0;
+#pragma unroll
+            for (int q = 0; q < kFidxEntries; ++q) ei = (q == i) ? e[q] : ei;
+            const uint32_t d = ei ^ fpw;
+            if (d - 1u >= mask) continue;
+            if (!skipped) {  // the first one has been tried
+                skipped = true;
+                continue;
+            }
+            if (flow2_probe_unit(T, d - 1u, k, tag, v6, c, rhi, rlo)) return true;
+        }
+    }
+    return false;
+}
+__device__ __forceinline__ bool flow2_lookup(const DevTables& T, const Key& k, uint32_t& rhi, uint32_t& rlo) {
+    const bool v6 = k.ip_ver == 6;
+    const uint32_t meta20 = k.meta & 0xFFFFFu, tag = meta20 | kSlotValid | (v6 ? kSlotV6 : 0u);
+    uint32_t x, y;
+    flow6_hash(k.sip, k.dip, k.ports, flow2_meta(meta20, v6), T.S2, x, y);
+    const uint32_t mask = (1u << T.fidx_bits) - 1u;
+    const uint32_t fpw = (flow_fp(x, y, T.S2 + 10) >> T.fidx_bits) << T.fidx_bits;
+    const uint32_t c[4] = {k.sip[0], v6 ? k.sip[1] : k.dip[0], v6 ? k.sip[2] : 0u, v6 ? k.sip[3] : 0u};
+    const uint32_t b0 = flow_bucket(x, y, 0, T.S2 + 10, T.fidx_nbuckets);
+    uint32_t overflow;
+    if (flow2_probe_bucket(T, b0, fpw, mask, k, tag, v6, c, rhi, rlo, overflow)) return true;
+    if (!overflow) return false;
+    const uint32_t b1 = flow_bucket(x, y, 1, T.S2 + 10, T.fidx_nbuckets);
+    if (b1 == b0) return false;
+    uint32_t unused;
+    return flow2_probe_bucket(T, b1, fpw, mask, k, tag, v6, c, rhi, rlo, unused);
+}
+
 // ------------------------------------------------------------------ stage 4: LPM ---------
 __device__ __forceinline__ uint32_t lpm_word_mask(uint32_t len, int i) {  // bits of word i covered by /len
     const int bits = (int)len - 32 * i;
@@ -405,7 +483,7 @@ struct SmemLayout {
                                   STAGES * (int)sizeof(StageInfo) + (TILE / 32) * 8 + 1024;
 };
 
-template <int TILE, int STAGES, bool COUNTERS, bool ACL, bool MULTI = false, int OCC = 0>
+template <int TILE, int STAGES, bool COUNTERS, bool ACL, bool MULTI = false, int OCC = 0, int FMT = 1>
 #ifndef SFC_MINB
 #define SFC_MINB 1
 #endif
@@ -414,7 +492,7 @@ template <int TILE, int STAGES, bool COUNTERS, bool ACL, bool MULTI = false, int
 #endif
 // OCC = 5: the same code held to 40 registers so that five CTAs share an SM — slower where the table is in L1
 // (more instructions), faster where probes wait on L2 / DRAM (api.cu picks per committed table).
-__global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS) ? SFC_MINB_ACL : SFC_MINB)) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
+__global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS || FMT == 2) ? SFC_MINB_ACL : SFC_MINB)) classify_kernel(const __grid_constant__ CUtensorMap hdr_map,
                                                               const uint16_t* __restrict__ in_port,
                                                               uint64_t* __restrict__ result, uint32_t n,
                                                               uint32_t n_tiles, uint32_t* ticket,
@@ -615,7 +693,7 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS) ? SF
                 };
                 for (uint32_t t = 0; t < T.acl_ntrees; ++t) {
                     uint4 e = T.acl_roots[t];
-                    while (!(e.x & kAclLeafBit)) {  // one 16-byte load per level
+                    for (int lvl = 0; lvl < kAclMaxLevels && !(e.x & kAclLeafBit); ++lvl) {  // one 16-byte load per level
                         uint32_t idx = acl_key_bit(qb, e.y & 0xFFFFu, 0u);
                         idx = acl_key_bit(qb, e.y >> 16, idx);
                         idx = acl_key_bit(qb, e.z & 0xFFFFu, idx);
@@ -624,6 +702,7 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS) ? SF
                         idx = acl_key_bit(qb, e.w >> 16, idx);
                         e = __ldg(T.acl_nodes + (e.x + idx));
                     }
+                    if (!(e.x & kAclLeafBit)) continue;  // deeper than any tree the builder makes: a damaged image, not a hang
                     // the first six candidates travel in the entry itself; they are tried two at a time so
                     // that the rule sectors of a pair are in flight together
                     const uint32_t cw[3] = {e.y, e.z, e.w};
@@ -681,10 +760,14 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS) ? SF
         if (!done && is_ip) {
             uint32_t h = 0, l = 0;
             bool hit = false;
-            if (k.ip_ver == 4) {
-                if (T.flow4_count) hit = flow4_lookup(T, k, h, l);
-            } else if (T.flow6_count) {
-                hit = flow6_lookup(T, k, h, l);
+            if constexpr (FMT == (int)kFlowFormatIndexed) {  // the kernel is compiled once per flow table format
+                if (T.flow4_count | T.flow6_count) hit = flow2_lookup(T, k, h, l);
+            } else {
+                if (k.ip_ver == 4) {
+                    if (T.flow4_count) hit = flow4_lookup(T, k, h, l);
+                } else if (T.flow6_count) {
+                    hit = flow6_lookup(T, k, h, l);
+                }
             }
             if (hit) {
                 rhi = h;

@@ -100,6 +100,31 @@ SFC_HD void expand_seed(uint64_t seed, uint32_t* out, int n) {
     for (int i = 0; i < n; ++i) out[i] = (uint32_t)(draw(seed, (uint64_t)i) >> 16) | 1u;
 }
 
+// ---------------------------------------------------------------- flow table, format 2 ----
+// "Indexed" format: one fingerprint index for both families in front of a dense record array, so that
+// what a lookup touches is small enough to stay in L2 (and, for small rule sets, in L1):
+//   index   buckets of one 32-byte sector: 7 entries + 1 overflow word.  entry = 0 (empty) or
+//           fp << B | (unit + 1), B = header.fidx_bits, fp = the top 32 - B bits of flow_fp().  Two
+//           bucket choices; a flow sits in its first choice unless that was full.  Word 7 counts the
+//           flows whose first choice is this bucket but which live in their second one: a lookup
+//           goes on to the second bucket only when that count is not zero (misses cost one sector).
+//   records 32-byte units.  IPv4: one unit [tag, ports, res_hi, res_lo, sip, dip, 0, 0].  IPv6: two
+//           consecutive units [tag, ports, res_hi, res_lo, sip0..3] [dip0..3, 0, 0, 0, 0].
+//           tag = proto | vlan << 8 | kSlotV6 (IPv6) | kSlotValid.
+// The hash is flow6_hash over the full key (IPv4 addresses in word 0, the rest zero) for both families.
+constexpr uint32_t kSlotV6 = 0x40000000u;
+constexpr int kFidxEntries = 7;
+constexpr int kFidxBucketWords = 8;
+constexpr int kFrecUnitWords = 8;
+constexpr uint32_t kFlowFormatSector = 1, kFlowFormatIndexed = 2;
+constexpr uint64_t kFlowIndexedMaxUnits = 3ull << 20;  // format chosen by size: up to ~100 MB of records use the index
+SFC_HD uint32_t flow_fp(uint32_t x, uint32_t y, const uint32_t* T) {  // T = the six bucket-choice seed words
+    uint64_t F = mul_wide(x ^ T[4], y ^ T[5]);
+    return (uint32_t)F ^ (uint32_t)(F >> 32);
+}
+// meta word fed to the hash: proto | vlan << 8 | (IPv6 ? 1 << 20 : 0)
+SFC_HD uint32_t flow2_meta(uint32_t meta20, bool v6) { return meta20 | (v6 ? 0x100000u : 0u); }
+
 // ---------------------------------------------------------------- L2 steering ------------
 // exact table: open addressing, linear probing, 16-byte entries; res_hi == 0 marks an empty entry
 struct L2Entry {
@@ -170,12 +195,13 @@ constexpr int kAclKeyRows = 12;  // 11 key words + the zero row
 constexpr uint32_t kAclZeroField = 11u * 128u;
 constexpr int kAclRuleWords = 24;
 constexpr int kAclMaxTrees = 8;
+constexpr int kAclMaxLevels = 16;  // the builder stops at depth 12; the kernel never walks further than this
 constexpr uint32_t kAclLeafBit = 0x80000000u, kAclMoreBit = 0x40000000u, kAclOffMask = 0x0FFFFFFFu;
 constexpr uint16_t kAclNeedG1 = 1u << 12, kAclNeedG2 = 1u << 13, kAclRankMask = 0x0FFFu, kAclNone = 0xFFFFu;
 
 // ---------------------------------------------------------------- image ------------------
 constexpr uint64_t kImageMagic = 0x3130434653303042ull;  // "B00SFC01"
-constexpr uint32_t kImageVersion = 11;
+constexpr uint32_t kImageVersion = 12;
 constexpr size_t kImageAlign = 256;
 
 struct ImageHeader {
@@ -214,6 +240,18 @@ struct ImageHeader {
     // slots per flow bucket: 1 (one sector per probe: tiny and huge tables) or 2 (dense tables that fit
     // in L2 only when packed); a table is nbuckets * slots slots, slot s of bucket b at index b * slots + s
     uint32_t flow4_slots, flow6_slots;
+
+    // flow table format: kFlowFormatSector (the two per-family cuckoo tables above) or kFlowFormatIndexed
+    // (fidx_* / frec_*; the flow4_* / flow6_* sections are then empty apart from the counts)
+    uint32_t flow_format, fidx_bits;
+    uint64_t fidx_off, fidx_seed, frec_off;
+    uint32_t fidx_nbuckets, frec_units;  // frec_units: capacity of the record array in 32-byte units (+1 pad unit follows)
+    uint32_t frec_used, fidx_first;      // units handed out so far (high-water mark); flows sitting in their first bucket
+
+    // L2 steering tables exist twice (copy 0 / copy 1) so that a commit can rebuild the idle copy while
+    // launches read the active one; l2x_off / l2w_off above always describe the ACTIVE copy
+    uint64_t l2x_copy_off[2], l2w_copy_off[2];
+    uint32_t l2x_cap, l2_active;
 };
 static_assert(sizeof(ImageHeader) <= 512, "image header grew past its reserved 512 bytes");
 constexpr size_t kImageHeaderBytes = 512;

@@ -272,6 +272,206 @@ uint32_t FlowTable::count_first() const {
     return n;
 }
 
+
+// ------------------------------------------------------------------ IndexedFlows ---------
+namespace {
+// one or two record units for a flow (format 2); returns the number of units
+int encode_units(const FlowRec& f, uint32_t next_nf, uint32_t* u) {
+    const bool six = f.ip_ver == 6;
+    for (int w = 0; w < 2 * kFrecUnitWords; ++w) u[w] = 0;
+    u[0] = (f.meta & 0xFFFFFu) | kSlotValid | (six ? kSlotV6 : 0u);
+    u[1] = f.ports;
+    u[2] = res_hi(f.action, next_nf, f.out_port);
+    u[3] = res_lo(SFC_STAGE_FLOW, f.id);
+    if (!six) {
+        u[4] = f.sip[0];
+        u[5] = f.dip[0];
+        return 1;
+    }
+    for (int w = 0; w < 4; ++w) {
+        u[4 + w] = f.sip[w];
+        u[8 + w] = f.dip[w];
+    }
+    return 2;
+}
+}  // namespace
+
+IndexedFlows::Where IndexedFlows::where(const uint32_t* sip, const uint32_t* dip, uint32_t ports, uint32_t meta20,
+                                        bool v6) const {
+    uint32_t x, y;
+    flow6_hash(sip, dip, ports, flow2_meta(meta20, v6), S, x, y);
+    Where w;
+    w.b0 = flow_bucket(x, y, 0, S + 10, nbuckets);
+    w.b1 = flow_bucket(x, y, 1, S + 10, nbuckets);
+    w.fp = flow_fp(x, y, S + 10) >> bits;
+    return w;
+}
+
+IndexedFlows::Where IndexedFlows::where_of_unit(uint32_t unit) const {
+    const uint32_t* u = rec + (size_t)unit * kFrecUnitWords;
+    const bool six = (u[0] & kSlotV6) != 0;
+    uint32_t sip[4] = {u[4], 0, 0, 0}, dip[4] = {u[5], 0, 0, 0};
+    if (six)
+        for (int w = 0; w < 4; ++w) {
+            sip[w] = u[4 + w];
+            dip[w] = u[8 + w];
+        }
+    return where(sip, dip, u[1], u[0] & 0xFFFFFu, six);
+}
+
+int64_t IndexedFlows::find(const FlowRec& f, uint32_t* bucket, int* slot) const {
+    if (!nbuckets) return -1;
+    const bool six = f.ip_ver == 6;
+    const Where w = where(f.sip, f.dip, f.ports, f.meta & 0xFFFFFu, six);
+    const uint32_t mask = (1u << bits) - 1u, tag = (f.meta & 0xFFFFFu) | kSlotValid | (six ? kSlotV6 : 0u);
+    const uint32_t bs[2] = {w.b0, w.b1};
+    for (int j = 0; j < (w.b1 == w.b0 ? 1 : 2); ++j) {
+        const uint32_t* b = idx + (size_t)bs[j] * kFidxBucketWords;
+        for (int s = 0; s < kFidxEntries; ++s) {
+            const uint32_t d = b[s] ^ (w.fp << bits);
+            if (d - 1u >= mask) continue;  // empty, or another fingerprint
+            const uint32_t unit = d - 1u;
+            const uint32_t* u = rec + (size_t)unit * kFrecUnitWords;
+            bool eq = u[0] == tag && u[1] == f.ports;
+            if (!six) eq = eq && u[4] == f.sip[0] && u[5] == f.dip[0];
+            else
+                for (int k = 0; k < 4; ++k) eq = eq && u[4 + k] == f.sip[k] && u[8 + k] == f.dip[k];
+            if (eq) {
+                if (bucket) *bucket = bs[j];
+                if (slot) *slot = s;
+                return unit;
+            }
+        }
+    }
+    return -1;
+}
+
+long IndexedFlows::room() const {
+    const long by_index = (long)nbuckets * kFidxEntries * 85 / 100 - (long)count;
+    const long by_units = ((long)units - (long)used) / 2 + (long)free2.size();  // worst case: every new flow is IPv6
+    return std::min(by_index, by_units);
+}
+
+// Put the entry for `unit` into one of its two buckets, moving residents out of the way if both are full.
+bool IndexedFlows::place(uint32_t unit, Where w, std::vector<uint32_t>* dirty) {
+    uint32_t came_from = 0xFFFFFFFFu;
+    for (int kick = 0; kick < 500; ++kick) {
+        const uint32_t e = (w.fp << bits) | (unit + 1u);
+        const uint32_t bs[2] = {w.b0, w.b1};
+        for (int j = 0; j < (w.b1 == w.b0 ? 1 : 2); ++j) {
+            uint32_t* b = idx + (size_t)bs[j] * kFidxBucketWords;
+            for (int s = 0; s < kFidxEntries; ++s)
+                if (!b[s]) {
+                    b[s] = e;
+                    touch_idx(bs[j], dirty);
+                    if (j == 1) {
+                        ++idx[(size_t)w.b0 * kFidxBucketWords + kFidxEntries];
+                        touch_idx(w.b0, dirty);
+                        ++second;
+                    }
+                    return true;
+                }
+        }
+        // both full: take the place of a resident that can move, and go on with that one
+        rng = mix64(rng + kGamma);
+        uint32_t B = (rng & 1) ? w.b1 : w.b0;
+        if (B == came_from) B = B == w.b0 ? w.b1 : w.b0;
+        uint32_t* b = idx + (size_t)B * kFidxBucketWords;
+        int s = -1;
+        Where vw{};
+        uint32_t vunit = 0;
+        for (int t = 0; t < kFidxEntries && s < 0; ++t) {
+            const int cand = (int)(((rng >> 8) + (uint64_t)t) % kFidxEntries);
+            vunit = (b[cand] & ((1u << bits) - 1u)) - 1u;
+            vw = where_of_unit(vunit);
+            if (vw.b0 != vw.b1) s = cand;
+        }
+        if (s < 0) return false;
+        b[s] = e;
+        touch_idx(B, dirty);
+        if (B != w.b0) {  // the newcomer lives in its second bucket
+            ++idx[(size_t)w.b0 * kFidxBucketWords + kFidxEntries];
+            touch_idx(w.b0, dirty);
+            ++second;
+        }
+        if (B != vw.b0) {  // the resident leaves its second bucket
+            --idx[(size_t)vw.b0 * kFidxBucketWords + kFidxEntries];
+            touch_idx(vw.b0, dirty);
+            --second;
+        }
+        // the resident must now go to its other bucket: express that as "both choices are that bucket"
+        const uint32_t other = B == vw.b0 ? vw.b1 : vw.b0;
+        const bool other_is_second = other != vw.b0;
+        came_from = B;
+        unit = vunit;
+        // try the other bucket directly; if it is full the loop kicks from there
+        uint32_t* ob = idx + (size_t)other * kFidxBucketWords;
+        bool placed = false;
+        for (int t = 0; t < kFidxEntries && !placed; ++t)
+            if (!ob[t]) {
+                ob[t] = (vw.fp << bits) | (vunit + 1u);
+                touch_idx(other, dirty);
+                placed = true;
+            }
+        if (placed) {
+            if (other_is_second) {
+                ++idx[(size_t)vw.b0 * kFidxBucketWords + kFidxEntries];
+                touch_idx(vw.b0, dirty);
+                ++second;
+            }
+            return true;
+        }
+        w = vw;  // continue: the evicted flow looks for room, not back where it came from
+    }
+    return false;
+}
+
+bool IndexedFlows::insert(const FlowRec& f, uint32_t next_nf, std::vector<uint32_t>* dirty) {
+    uint32_t u[2 * kFrecUnitWords];
+    const int n = encode_units(f, next_nf, u);
+    uint32_t unit;
+    if (n == 1 && !free1.empty()) {
+        unit = free1.back();
+        free1.pop_back();
+    } else if (n == 2 && !free2.empty()) {
+        unit = free2.back();
+        free2.pop_back();
+    } else if (n == 1 && !free2.empty()) {  // split a released pair
+        unit = free2.back();
+        free2.pop_back();
+        free1.push_back(unit + 1);
+    } else {
+        if (used + (uint32_t)n > units) return false;
+        unit = used;
+        used += (uint32_t)n;
+    }
+    memcpy(rec + (size_t)unit * kFrecUnitWords, u, (size_t)n * kFrecUnitWords * 4);
+    for (int k = 0; k < n; ++k) touch_rec(unit + (uint32_t)k, dirty);
+    ++count;
+    return place(unit, where(f.sip, f.dip, f.ports, f.meta & 0xFFFFFu, f.ip_ver == 6), dirty);
+}
+
+bool IndexedFlows::erase(const FlowRec& f, std::vector<uint32_t>* dirty) {
+    uint32_t bucket = 0;
+    int slot = 0;
+    const int64_t unit = find(f, &bucket, &slot);
+    if (unit < 0) return false;
+    const Where w = where(f.sip, f.dip, f.ports, f.meta & 0xFFFFFu, f.ip_ver == 6);
+    idx[(size_t)bucket * kFidxBucketWords + slot] = 0;
+    touch_idx(bucket, dirty);
+    if (bucket != w.b0) {
+        --idx[(size_t)w.b0 * kFidxBucketWords + kFidxEntries];
+        touch_idx(w.b0, dirty);
+        --second;
+    }
+    const int n = f.ip_ver == 6 ? 2 : 1;
+    memset(rec + (size_t)unit * kFrecUnitWords, 0, (size_t)n * kFrecUnitWords * 4);
+    for (int k = 0; k < n; ++k) touch_rec((uint32_t)unit + (uint32_t)k, dirty);
+    (n == 2 ? free2 : free1).push_back((uint32_t)unit);
+    --count;
+    return true;
+}
+
 // ------------------------------------------------------------------ image assembly -------
 namespace {
 
@@ -297,7 +497,7 @@ bool build_cuckoo(Blob& blob, const RuleStore& rs, bool v6, const std::vector<co
     size_t n = recs.size();
     int nhash = rs.flow_hashes;
     int max_load = nhash == 2 ? 45 : 85;
-    int load_pct = std::min(std::max(rs.flow_load_pct, 5), max_load);
+    int load_pct = std::min(std::max(rs.flow_load_pct ? rs.flow_load_pct : 40, 5), max_load);
     // Slots per bucket.  One slot = one sector per probe, which is what counts when the table lives in
     // DRAM (B200 sustains ~50 G random sectors/s there whatever their size: tools/randgather.cu) and
     // costs nothing when it is small; it is the default.  Two slots at 80 % load (option "flow_slots" = 2)
@@ -340,6 +540,50 @@ bool build_cuckoo(Blob& blob, const RuleStore& rs, bool v6, const std::vector<co
         }
     }
     err = "flow table: cuckoo insertion did not converge";
+    return false;
+}
+
+// ---- indexed flow table (format 2) ---------------------------------------------------------
+bool build_indexed(Blob& blob, const RuleStore& rs, ImageHeader& H, std::string& err) {
+    const size_t n = rs.flows.size();
+    uint64_t units_needed = 0;
+    for (auto& f : rs.flows) units_needed += f.ip_ver == 6 ? 2 : 1;
+    int load_pct = rs.flow_load_pct ? std::min(std::max(rs.flow_load_pct, 5), 85) : 65;
+    uint64_t nb = std::max<uint64_t>(1, (n * 100 + (uint64_t)load_pct * kFidxEntries - 1) / ((uint64_t)load_pct * kFidxEntries));
+    const uint64_t units = units_needed + units_needed / 8 + 8192;  // room for flows added later
+    uint32_t bits = 1;
+    while ((1ull << bits) <= units + 1) ++bits;  // entries hold unit + 1
+    std::vector<uint8_t> nf(SFC_MAX_PORTS, (uint8_t)SFC_NF_NONE);
+    for (uint32_t p = 0; p < SFC_MAX_PORTS; ++p) nf[p] = nf_of_port(rs, p);
+    for (int attempt = 0; attempt < 6; ++attempt, nb = nb + nb / 8 + 1) {
+        size_t start = blob.img.size();
+        H.fidx_off = blob.reserve((size_t)nb * kFidxBucketWords * 4, 0);
+        H.frec_off = blob.reserve((size_t)(units + 1) * kFrecUnitWords * 4, 0);
+        IndexedFlows t;
+        t.idx = blob.at<uint32_t>(H.fidx_off);
+        t.rec = blob.at<uint32_t>(H.frec_off);
+        t.nbuckets = (uint32_t)nb;
+        t.bits = bits;
+        t.units = (uint32_t)units;
+        const uint64_t seed = mix64(0x5FC0C0DEull + 131ull * attempt + 3ull);
+        expand_seed(seed, t.S, kFlow6SeedWords);
+        bool ok = true;
+        for (size_t i = 0; i < n && ok; ++i) {
+            const FlowRec& f = rs.flows[i];
+            ok = t.insert(f, f.action == SFC_ACT_FORWARD ? nf[f.out_port] : (uint32_t)SFC_NF_NONE, nullptr);
+        }
+        if (ok) {
+            H.fidx_nbuckets = (uint32_t)nb;
+            H.fidx_bits = bits;
+            H.fidx_seed = seed;
+            H.frec_units = (uint32_t)units;
+            H.frec_used = t.used;
+            H.fidx_first = t.count - t.second;
+            return true;
+        }
+        blob.img.resize(start);
+    }
+    err = "flow table: index insertion did not converge";
     return false;
 }
 
@@ -728,6 +972,71 @@ void build_acl(Blob& blob, const std::vector<AclRec>& recs, ImageHeader& H) {
 
 }  // namespace
 
+// Resolve the OpenFlow priorities per match (exact and wildcard apart) and write the two tables of copy
+// `copy`; the header inside `image` gets the new counts and its active-copy fields.  Returns false if
+// the exact rules no longer fit (load above one half).
+static bool fill_l2_copy(const RuleStore& rs, uint8_t* image, int copy, std::vector<uint32_t>* dirty) {
+    ImageHeader H;
+    memcpy(&H, image, sizeof(H));
+    std::map<std::pair<uint32_t, uint32_t>, const L2Rule*> exact;  // (key_hi,key_lo) -> winner
+    std::map<uint16_t, const L2Rule*> wild;
+    auto better = [](const L2Rule* a, const L2Rule* b) {  // a beats b
+        return a->priority > b->priority || (a->priority == b->priority && a->id < b->id);
+    };
+    for (auto& r : rs.l2) {
+        if (r.has_mac) {
+            uint32_t hi = ((uint32_t)r.in_port << 16) | ((uint32_t)r.mac[0] << 8) | r.mac[1];
+            uint32_t lo = be32(r.mac + 2);
+            auto key = std::make_pair(hi, lo);
+            auto it = exact.find(key);
+            if (it == exact.end() || better(&r, it->second)) exact[key] = &r;
+        } else {
+            auto it = wild.find(r.in_port);
+            if (it == wild.end() || better(&r, it->second)) wild[r.in_port] = &r;
+        }
+    }
+    if (exact.size() * 2 > H.l2x_cap) return false;
+    std::vector<L2Entry> x(H.l2x_cap, L2Entry{0, 0, 0, 0});
+    std::vector<L2Wild> w(H.l2w_n, L2Wild{0, 0});
+    for (auto& kv : exact) {
+        uint32_t i = l2_hash(kv.first.first, kv.first.second) & H.l2x_mask;
+        while (x[i].res_hi) i = (i + 1) & H.l2x_mask;
+        x[i].key_hi = kv.first.first;
+        x[i].key_lo = kv.first.second;
+        x[i].res_lo = res_lo(SFC_STAGE_L2_EXACT, kv.second->id);
+        x[i].res_hi = res_hi(SFC_ACT_FORWARD, nf_of_port(rs, kv.second->out_port), kv.second->out_port);
+    }
+    for (auto& kv : wild) {
+        if (kv.first >= H.l2w_n) continue;
+        w[kv.first].res_hi = res_hi(SFC_ACT_FORWARD, nf_of_port(rs, kv.second->out_port), kv.second->out_port);
+        w[kv.first].res_lo = res_lo(SFC_STAGE_L2_WILD, kv.second->id);
+    }
+    // write sector by sector, reporting the sectors whose bytes changed
+    auto put = [&](uint64_t off, const void* src, size_t bytes) {
+        const uint8_t* p = (const uint8_t*)src;
+        for (size_t o = 0; o < bytes; o += 32) {
+            const size_t m = std::min<size_t>(32, bytes - o);
+            if (memcmp(image + off + o, p + o, m)) {
+                memcpy(image + off + o, p + o, m);
+                if (dirty) dirty->push_back((uint32_t)((off + o) / 32));
+            }
+        }
+    };
+    put(H.l2x_copy_off[copy], x.data(), x.size() * sizeof(L2Entry));
+    put(H.l2w_copy_off[copy], w.data(), w.size() * sizeof(L2Wild));
+    H.l2_active = (uint32_t)copy;
+    H.l2x_off = H.l2x_copy_off[copy];
+    H.l2w_off = H.l2w_copy_off[copy];
+    H.l2x_count = (uint32_t)exact.size();
+    H.l2w_count = (uint32_t)wild.size();
+    memcpy(image, &H, sizeof(H));
+    return true;
+}
+
+bool rebuild_l2_copy(const RuleStore& rs, uint8_t* image, int copy, std::vector<uint32_t>* dirty) {
+    return fill_l2_copy(rs, image, copy, dirty);
+}
+
 bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& image, std::string& err) {
     image.clear();
     image.resize(kImageHeaderBytes, 0);
@@ -745,52 +1054,49 @@ bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& imag
     H.flow4_count = (uint32_t)f4.size();
     H.flow6_count = (uint32_t)f6.size();
     H.flow4_nhash = H.flow6_nhash = (uint32_t)rs.flow_hashes;
-    if (!build_cuckoo(blob, rs, false, f4, H.flow4_off, H.flow4_nbuckets, H.flow4_slots, H.flow4_seed, H.flow4_first, err)) return false;
-    if (!build_cuckoo(blob, rs, true, f6, H.flow6_off, H.flow6_nbuckets, H.flow6_slots, H.flow6_seed, H.flow6_first, err)) return false;
+    // Format: the indexed table keeps what a lookup touches small (7 index bytes and one 32-byte record per
+    // IPv4 flow) and serves both families with one code path; the sector tables cost one sector per probe
+    // and nothing else, which is what counts once the records cannot stay in L2 anyway.
+    const uint64_t units_needed = (uint64_t)f4.size() + 2ull * f6.size();
+    uint32_t format = (uint32_t)rs.flow_format;
+    if (format != kFlowFormatSector && format != kFlowFormatIndexed)
+        format = units_needed <= kFlowIndexedMaxUnits ? kFlowFormatIndexed : kFlowFormatSector;
+    if (format == kFlowFormatIndexed && units_needed + units_needed / 8 + 8192 >= (1ull << 27)) format = kFlowFormatSector;
+    H.flow_format = format;
+    if (format == kFlowFormatIndexed) {
+        std::vector<const FlowRec*> none;
+        H.flow4_count = H.flow6_count = 0;  // the sector tables stay empty (8 buckets each); counts are restored below
+        if (!build_cuckoo(blob, rs, false, none, H.flow4_off, H.flow4_nbuckets, H.flow4_slots, H.flow4_seed, H.flow4_first, err)) return false;
+        if (!build_cuckoo(blob, rs, true, none, H.flow6_off, H.flow6_nbuckets, H.flow6_slots, H.flow6_seed, H.flow6_first, err)) return false;
+        H.flow4_count = (uint32_t)f4.size();
+        H.flow6_count = (uint32_t)f6.size();
+        if (!build_indexed(blob, rs, H, err)) return false;
+    } else {
+        if (!build_cuckoo(blob, rs, false, f4, H.flow4_off, H.flow4_nbuckets, H.flow4_slots, H.flow4_seed, H.flow4_first, err)) return false;
+        if (!build_cuckoo(blob, rs, true, f6, H.flow6_off, H.flow6_nbuckets, H.flow6_slots, H.flow6_seed, H.flow6_first, err)) return false;
+        H.fidx_off = H.frec_off = blob.reserve(64, 0);
+        H.fidx_nbuckets = 1;
+        H.fidx_bits = 1;
+        H.frec_units = 1;
+    }
 
-    // L2 steering: resolve OpenFlow priorities per match, exact and wildcard apart
+    // L2 steering: two copies of the exact and the wildcard table, with room to grow, so that later rule
+    // edits are rebuilt into the idle copy instead of rebuilding the image (rebuild_l2_copy)
     {
-        std::map<std::pair<uint32_t, uint32_t>, const L2Rule*> exact;  // (key_hi,key_lo) -> winner
-        std::map<uint16_t, const L2Rule*> wild;
-        auto better = [](const L2Rule* a, const L2Rule* b) {  // a beats b
-            return a->priority > b->priority || (a->priority == b->priority && a->id < b->id);
-        };
-        uint32_t max_port = 0;
-        for (auto& r : rs.l2) {
-            max_port = std::max<uint32_t>(max_port, r.in_port);
-            if (r.has_mac) {
-                uint32_t hi = ((uint32_t)r.in_port << 16) | ((uint32_t)r.mac[0] << 8) | r.mac[1];
-                uint32_t lo = be32(r.mac + 2);
-                auto key = std::make_pair(hi, lo);
-                auto it = exact.find(key);
-                if (it == exact.end() || better(&r, it->second)) exact[key] = &r;
-            } else {
-                auto it = wild.find(r.in_port);
-                if (it == wild.end() || better(&r, it->second)) wild[r.in_port] = &r;
-            }
-        }
-        uint32_t cap = 16;
-        while (cap < exact.size() * 2) cap <<= 1;
+        size_t n_exact = 0;
+        for (auto& r : rs.l2) n_exact += r.has_mac;
+        uint32_t cap = 256;
+        while (cap < n_exact * 4) cap <<= 1;
+        H.l2x_cap = cap;
         H.l2x_mask = cap - 1;
-        H.l2x_count = (uint32_t)exact.size();
-        H.l2x_off = blob.reserve((size_t)cap * sizeof(L2Entry), 0);
-        for (auto& kv : exact) {
-            L2Entry* tab = blob.at<L2Entry>(H.l2x_off);
-            uint32_t i = l2_hash(kv.first.first, kv.first.second) & H.l2x_mask;
-            while (tab[i].res_hi) i = (i + 1) & H.l2x_mask;
-            tab[i].key_hi = kv.first.first;
-            tab[i].key_lo = kv.first.second;
-            tab[i].res_lo = res_lo(SFC_STAGE_L2_EXACT, kv.second->id);
-            tab[i].res_hi = res_hi(SFC_ACT_FORWARD, nf_of_port(rs, kv.second->out_port), kv.second->out_port);
+        H.l2w_n = SFC_MAX_PORTS;
+        for (int c = 0; c < 2; ++c) {
+            H.l2x_copy_off[c] = blob.reserve((size_t)cap * sizeof(L2Entry), 0);
+            H.l2w_copy_off[c] = blob.reserve((size_t)H.l2w_n * sizeof(L2Wild), 0);
         }
-        H.l2w_n = rs.l2.empty() ? 1 : max_port + 1;
-        H.l2w_count = (uint32_t)wild.size();
-        H.l2w_off = blob.reserve((size_t)H.l2w_n * sizeof(L2Wild), 0);
-        for (auto& kv : wild) {
-            L2Wild* w = blob.at<L2Wild>(H.l2w_off);
-            w[kv.first].res_hi = res_hi(SFC_ACT_FORWARD, nf_of_port(rs, kv.second->out_port), kv.second->out_port);
-            w[kv.first].res_lo = res_lo(SFC_STAGE_L2_WILD, kv.second->id);
-        }
+        memcpy(image.data(), &H, sizeof(H));  // fill_l2_copy reads the capacities from the header in the image
+        fill_l2_copy(rs, image.data(), 0, nullptr);
+        memcpy(&H, image.data(), sizeof(H));
     }
     build_lpm(blob, rs, 4, rs.lpm4, H.lpm4_root_off, H.lpm4_nodes_off, H.lpm4_nh_off, H.lpm4_nnodes, H.lpm4_count,
               H.lpm4_tail_off, H.lpm4_ntails);
@@ -831,6 +1137,36 @@ const char* validate_image(const uint8_t* img, size_t len) {
              inside(H.acl_rule_off, (uint64_t)H.acl_nrules * kAclRuleWords * 4) &&
              inside(H.acl_res_off, (uint64_t)H.acl_nrules * 4);
     if (!ok) return "image: a section lies outside the buffer or a field is out of range";
+    // the kernel reads these sections with 16- and 32-byte loads
+    const uint64_t offs32[] = {H.flow4_off, H.flow6_off, H.fidx_off, H.frec_off, H.lpm4_tail_off, H.lpm6_tail_off, H.acl_rule_off};
+    const uint64_t offs16[] = {H.l2x_off, H.l2w_off, H.acl_nodes_off, H.lpm4_root_off, H.lpm4_nodes_off, H.lpm6_root_off,
+                               H.lpm6_nodes_off, H.lpm4_nh_off, H.lpm6_nh_off, H.acl_leaf_off, H.acl_res_off};
+    for (uint64_t o : offs32)
+        if (o & 31) return "image: a section is not 32-byte aligned";
+    for (uint64_t o : offs16)
+        if (o & 15) return "image: a section is not 16-byte aligned";
+    // L2 exact table: linear probing ends at an empty entry, so there must be one
+    {
+        if ((uint64_t)H.l2x_count * 2 > (uint64_t)H.l2x_mask + 1) return "image: the L2 exact table is more than half full";
+        const L2Entry* x = (const L2Entry*)(img + H.l2x_off);
+        uint32_t used = 0;
+        for (uint64_t i = 0; i <= H.l2x_mask; ++i) used += x[i].res_hi != 0;
+        if (used > ((uint64_t)H.l2x_mask + 1) / 2) return "image: the L2 exact table has too few empty entries";
+    }
+    if (H.flow_format != kFlowFormatSector && H.flow_format != kFlowFormatIndexed) return "image: unknown flow table format";
+    if (H.flow_format == kFlowFormatIndexed) {
+        if (H.fidx_bits < 1 || H.fidx_bits > 27 || !H.fidx_nbuckets || ((uint64_t)H.frec_units + 1) >= (1ull << H.fidx_bits) ||
+            !inside(H.fidx_off, (uint64_t)H.fidx_nbuckets * kFidxBucketWords * 4) ||
+            !inside(H.frec_off, ((uint64_t)H.frec_units + 1) * kFrecUnitWords * 4))
+            return "image: the flow index or record section is out of range";
+        const uint32_t* e = (const uint32_t*)(img + H.fidx_off);
+        const uint32_t mask = (1u << H.fidx_bits) - 1u;
+        for (uint64_t b = 0; b < H.fidx_nbuckets; ++b)
+            for (int sl = 0; sl < kFidxEntries; ++sl) {
+                const uint32_t v = e[b * kFidxBucketWords + sl];
+                if (v && ((v & mask) == 0 || (v & mask) - 1u >= H.frec_units)) return "image: a flow index entry points outside the record array";
+            }
+    }
 
     // Everything the kernel follows as an index is checked here once, so that a damaged or hostile image
     // is refused on the host instead of faulting on the device.  Flow and L2 tables hold no indices.

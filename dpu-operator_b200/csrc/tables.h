@@ -88,6 +88,41 @@ struct FlowTable {
     static void encode(const FlowRec& f, uint32_t next_nf, uint32_t* rec);  // fills words() words
 };
 
+// The indexed flow table (format 2, see sfc_common.h) as plain host memory: a fingerprint index in front of
+// a dense record array, both families in one structure.  Like FlowTable it is used on the image being
+// assembled and as the host shadow of the committed image; every sector it writes is reported (as a
+// sector number relative to the start of the image) so that a commit can ship exactly those.
+struct IndexedFlows {
+    uint32_t* idx = nullptr;  // nbuckets buckets of kFidxBucketWords words
+    uint32_t* rec = nullptr;  // units + 1 units of kFrecUnitWords words
+    uint32_t nbuckets = 0, bits = 0, units = 0, used = 0;
+    uint32_t idx_sector0 = 0, rec_sector0 = 0;  // image sector numbers of idx[0] and rec[0]
+    uint32_t S[kFlow6SeedWords] = {0};
+    uint64_t rng = 0x7654321ull;
+    std::vector<uint32_t> free1, free2;  // released single units / unit pairs (first unit of the pair)
+    uint32_t count = 0, second = 0;      // flows stored; flows living in their second bucket
+
+    struct Where {
+        uint32_t b0, b1, fp;
+    };
+    Where where(const uint32_t* sip, const uint32_t* dip, uint32_t ports, uint32_t meta20, bool v6) const;
+    Where where_of_unit(uint32_t unit) const;  // recomputed from the record the unit holds
+    // returns the unit of the flow or -1; *bucket / *slot receive its index position
+    int64_t find(const FlowRec& f, uint32_t* bucket = nullptr, int* slot = nullptr) const;
+    bool insert(const FlowRec& f, uint32_t next_nf, std::vector<uint32_t>* dirty);
+    bool erase(const FlowRec& f, std::vector<uint32_t>* dirty);
+    long room() const;  // flows that can still be added before the table has to be rebuilt larger (approximate)
+
+  private:
+    bool place(uint32_t unit, Where w, std::vector<uint32_t>* dirty);
+    void touch_idx(uint32_t bucket, std::vector<uint32_t>* dirty) const {
+        if (dirty) dirty->push_back(idx_sector0 + bucket);
+    }
+    void touch_rec(uint32_t unit, std::vector<uint32_t>* dirty) const {
+        if (dirty) dirty->push_back(rec_sector0 + unit);
+    }
+};
+
 struct FlowChange {
     bool add;
     FlowRec rec;
@@ -107,7 +142,8 @@ struct RuleStore {
     FlowIndex flow_index;
     uint32_t next_flow_id = 0;
     std::vector<FlowChange> flow_log;  // flow edits since the last commit, in order
-    bool other_dirty = true;           // anything but flows changed since the last commit
+    bool l2_dirty = false;             // L2 steering rules changed since the last commit (rebuilt into the idle copy)
+    bool other_dirty = true;           // anything else changed since the last commit: the next commit rebuilds the image
     // LPM
     typedef std::array<uint32_t, 5> LpmKey;  // len, w[0..3]
     std::map<LpmKey, LpmRec> lpm4, lpm6;
@@ -116,9 +152,10 @@ struct RuleStore {
     std::vector<AclRec> acl;
     uint32_t next_acl_id = 0;
     // knobs
-    int flow_load_pct = 40;
+    int flow_load_pct = 0;  // 0 = the format's default (sector: 40, indexed: 65)
     int flow_hashes = 2;
     int flow_slots = 0;  // slots per flow bucket: 2 = dense two-slot buckets (see build_cuckoo), anything else = 1
+    int flow_format = 0;  // 0 = by size, kFlowFormatSector, kFlowFormatIndexed
 
     void clear_rules();
 };
@@ -128,6 +165,10 @@ bool flow_from_key(const sfc_flow_key& k, const sfc_flow_action& a, FlowRec& out
 
 // Build the image.  Returns false and sets err on failure (e.g. cuckoo build could not converge).
 bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& image, std::string& err);
+// Rebuild the L2 steering tables of copy `copy` (0 / 1) inside an existing image from the rule store and make
+// it the active one in the header.  Returns false if the rules no longer fit the capacity the image was built
+// with (the caller then rebuilds the image).  Sectors whose bytes changed are appended to *dirty.
+bool rebuild_l2_copy(const RuleStore& rs, uint8_t* image, int copy, std::vector<uint32_t>* dirty);
 uint8_t nf_of_port(const RuleStore& rs, uint32_t port);
 
 // Structural validation of an image received from elsewhere (import / broadcast).

@@ -23,7 +23,7 @@
 // The pinned stage order is SURVEY.md §8a "Proposed pinned semantics".  The rule *sets* are pinned
 // separately against the reference's generators in tests/test_replay.py.
 //
-// Deliberately plain: byte-at-a-time parser, std::unordered_map for exact matches, a linear
+// Deliberately plain: byte-at-a-time parser, std::unordered_map over the 40 key bytes for exact matches, a linear
 // priority scan for the ACL, a one-bit-per-level binary trie for LPM.  It shares no code with the
 // CUDA library (only the public structs of include/b200sfc.h).
 #include <algorithm>
@@ -148,19 +148,31 @@ struct BitTrie {
     }
 };
 
-std::string flow_key_bytes(uint8_t ip_ver, uint16_t vlan, uint8_t proto, const uint8_t* src, const uint8_t* dst,
-                           uint16_t sport, uint16_t dport) {
-    std::string s(40, '\0');
-    s[0] = (char)ip_ver;
-    s[1] = (char)proto;
-    s[2] = (char)(vlan >> 8);
-    s[3] = (char)vlan;
-    s[4] = (char)(sport >> 8);
-    s[5] = (char)sport;
-    s[6] = (char)(dport >> 8);
-    s[7] = (char)dport;
-    memcpy(&s[8], src, 16);
-    memcpy(&s[24], dst, 16);
+// exact-match key: the 40 bytes (ip_ver, proto, vlan, sport, dport, src, dst) as they are, hashed with FNV-1a
+struct FlowKey {
+    uint8_t b[40];
+    bool operator==(const FlowKey& o) const { return !memcmp(b, o.b, 40); }
+};
+struct FlowKeyHash {
+    size_t operator()(const FlowKey& k) const {
+        uint64_t h = 0xcbf29ce484222325ull;
+        for (int i = 0; i < 40; ++i) h = (h ^ k.b[i]) * 0x100000001b3ull;
+        return (size_t)(h ^ (h >> 29));
+    }
+};
+FlowKey flow_key_bytes(uint8_t ip_ver, uint16_t vlan, uint8_t proto, const uint8_t* src, const uint8_t* dst,
+                       uint16_t sport, uint16_t dport) {
+    FlowKey s;
+    s.b[0] = ip_ver;
+    s.b[1] = proto;
+    s.b[2] = (uint8_t)(vlan >> 8);
+    s.b[3] = (uint8_t)vlan;
+    s.b[4] = (uint8_t)(sport >> 8);
+    s.b[5] = (uint8_t)sport;
+    s.b[6] = (uint8_t)(dport >> 8);
+    s.b[7] = (uint8_t)dport;
+    memcpy(s.b + 8, src, 16);
+    memcpy(s.b + 24, dst, 16);
     return s;
 }
 
@@ -169,7 +181,7 @@ std::string flow_key_bytes(uint8_t ip_ver, uint16_t vlan, uint8_t proto, const u
 struct oracle {
     std::vector<L2Rule> l2;
     std::vector<uint16_t> nf_in, nf_out;
-    std::unordered_map<std::string, FlowVal> flows;
+    std::unordered_map<FlowKey, FlowVal, FlowKeyHash> flows;
     BitTrie lpm4, lpm6;
     bool has_lpm4 = false, has_lpm6 = false;
     std::vector<AclRule> acl;
@@ -308,8 +320,8 @@ void orc_lpm_add(oracle* o, int af, const uint8_t* prefix, int len, uint16_t por
 }
 void orc_acl_add(oracle* o, const sfc_acl_rule* r, uint32_t id) { o->acl.push_back(AclRule{*r, id}); }
 
-// classify n packets on `threads` host threads (contiguous split); counters may be NULL
-// (counters are only filled when threads == 1)
+// classify n packets on `threads` host threads (contiguous split); counters may be NULL, else they are
+// ADDED to (each thread counts into its own array, the arrays are summed at the end)
 void orc_classify(const oracle* o, const uint8_t* hdr, const uint16_t* in_port, uint64_t* result, size_t n,
                   int threads, uint64_t* counters) {
     if (threads <= 1) {
@@ -317,14 +329,18 @@ void orc_classify(const oracle* o, const uint8_t* hdr, const uint16_t* in_port, 
         return;
     }
     std::vector<std::thread> pool;
+    std::vector<std::vector<uint64_t>> cnt(counters ? threads : 0, std::vector<uint64_t>(SFC_CNT_TOTAL, 0));
     size_t per = (n + threads - 1) / threads;
     for (int t = 0; t < threads; ++t) {
         size_t lo = std::min(n, per * t), hi = std::min(n, lo + per);
+        uint64_t* mine = counters ? cnt[t].data() : nullptr;
         pool.emplace_back([=] {
-            for (size_t i = lo; i < hi; ++i) result[i] = o->classify_one(hdr + i * SFC_HDR_BYTES, in_port[i], nullptr);
+            for (size_t i = lo; i < hi; ++i) result[i] = o->classify_one(hdr + i * SFC_HDR_BYTES, in_port[i], mine);
         });
     }
     for (auto& th : pool) th.join();
+    for (auto& c : cnt)
+        for (size_t i = 0; i < SFC_CNT_TOTAL; ++i) counters[i] += c[i];
 }
 
 // expose the parser for unit tests: out = {vlan, ip_ver, proto, sport, dport}, addresses, dmac

@@ -17,94 +17,14 @@ if ROOT not in sys.path:
 sfc = importlib.import_module("dpu-operator_b200")
 consts = sfc.consts
 
-ORACLE_SO = os.path.join(ROOT, "oracle", "libsfc_oracle.so")
-
-
-def _load_oracle():
-    if not os.path.exists(ORACLE_SO):
-        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")])
-    L = C.CDLL(ORACLE_SO)
-    vp = C.c_void_p
-    L.orc_create.restype = vp
-    L.orc_destroy.argtypes = [vp]
-    L.orc_clear.argtypes = [vp]
-    L.orc_l2_add.argtypes = [vp, C.c_uint16, C.c_uint16, vp, C.c_uint32, C.c_uint32]
-    L.orc_l2_del.argtypes = [vp, C.c_uint16, vp]
-    L.orc_chain_set.argtypes = [vp, vp, vp, C.c_size_t]
-    L.orc_flow_add.argtypes = [vp, vp, vp, C.c_size_t, C.c_uint32]
-    L.orc_flow_del.argtypes = [vp, vp]
-    L.orc_lpm_add.argtypes = [vp, C.c_int, vp, C.c_int, C.c_uint16, C.c_uint32]
-    L.orc_acl_add.argtypes = [vp, vp, C.c_uint32]
-    L.orc_classify.argtypes = [vp, vp, vp, vp, C.c_size_t, C.c_int, vp]
-    L.orc_parse.argtypes = [vp, vp, vp, vp, vp]
-    return L
-
-
-olib = _load_oracle()
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import orc as _orc  # noqa: E402  (oracle bindings: no product code behind them)
+from orc import ORACLE_SO, Oracle, OracleGen, olib  # noqa: E402,F401
 from py_oracle import PyOracle  # noqa: E402
 
-
-def _macbuf(mac):
-    return None if mac is None else C.cast(C.create_string_buffer(bytes(mac), 6), C.c_void_p)
-
-
-class Oracle:
-    """ctypes view of oracle/libsfc_oracle.so."""
-
-    def __init__(self):
-        self._o = C.c_void_p(olib.orc_create())
-
-    def __del__(self):
-        if getattr(self, "_o", None):
-            olib.orc_destroy(self._o)
-            self._o = None
-
-    def l2_add(self, in_port, out_port, mac, priority, rid):
-        olib.orc_l2_add(self._o, in_port, out_port, _macbuf(mac), priority, rid)
-
-    def l2_del(self, in_port, mac=None):
-        olib.orc_l2_del(self._o, in_port, _macbuf(mac))
-
-    def chain_set(self, ins, outs):
-        a = np.ascontiguousarray(ins, dtype=np.uint16)
-        b = np.ascontiguousarray(outs, dtype=np.uint16)
-        olib.orc_chain_set(self._o, a.ctypes.data, b.ctypes.data, a.size)
-
-    def flow_add(self, keys, acts, first_id):
-        keys = np.ascontiguousarray(keys, dtype=sfc.FLOW_KEY_DTYPE)
-        acts = np.ascontiguousarray(acts, dtype=sfc.FLOW_ACTION_DTYPE)
-        olib.orc_flow_add(self._o, keys.ctypes.data, acts.ctypes.data, keys.size, first_id)
-
-    def flow_del(self, key):
-        k = np.ascontiguousarray(key, dtype=sfc.FLOW_KEY_DTYPE).reshape(1)
-        olib.orc_flow_del(self._o, k.ctypes.data)
-
-    def lpm_add(self, af, prefix, length, port, pid):
-        buf = C.create_string_buffer(bytes(prefix).ljust(16, b"\0"), 16)
-        olib.orc_lpm_add(self._o, af, C.cast(buf, C.c_void_p), length, port, pid)
-
-    def acl_add(self, rule, rid):
-        r = np.ascontiguousarray(rule, dtype=sfc.ACL_RULE_DTYPE).reshape(1)
-        olib.orc_acl_add(self._o, r.ctypes.data, rid)
-
-    def classify(self, hdr, in_port, threads=1, counters=False):
-        hdr = np.ascontiguousarray(hdr, dtype=np.uint8)
-        in_port = np.ascontiguousarray(in_port, dtype=np.uint16)
-        out = np.empty(in_port.size, dtype=np.uint64)
-        cnt = np.zeros(consts.CNT_TOTAL, dtype=np.uint64) if counters else None
-        olib.orc_classify(self._o, hdr.ctypes.data, in_port.ctypes.data, out.ctypes.data, in_port.size, threads,
-                          cnt.ctypes.data if counters else None)
-        return (out, cnt) if counters else out
-
-    @staticmethod
-    def parse(hdr_row):
-        h = np.ascontiguousarray(hdr_row, dtype=np.uint8)
-        f = np.zeros(5, dtype=np.uint32)
-        s, d, m = np.zeros(16, np.uint8), np.zeros(16, np.uint8), np.zeros(6, np.uint8)
-        olib.orc_parse(h.ctypes.data, f.ctypes.data, s.ctypes.data, d.ctypes.data, m.ctypes.data)
-        return dict(vlan=int(f[0]), ver=int(f[1]), proto=int(f[2]), sport=int(f[3]), dport=int(f[4]),
-                    src=bytes(s), dst=bytes(d), dmac=bytes(m))
+assert _orc.FLOW_KEY_DTYPE == sfc.FLOW_KEY_DTYPE and _orc.FLOW_ACTION_DTYPE == sfc.FLOW_ACTION_DTYPE
+assert _orc.ACL_RULE_DTYPE == sfc.ACL_RULE_DTYPE and _orc.GEN_SPEC_DTYPE == sfc.GEN_SPEC_DTYPE
+assert _orc.CNT_TOTAL == consts.CNT_TOTAL
 
 
 def _prio(in_port, out_port, mac):

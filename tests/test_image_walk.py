@@ -27,13 +27,13 @@ def expand_seed(seed, n):
 
 
 class Image:
-    """Field offsets follow struct ImageHeader (version 11)."""
+    """Field offsets follow struct ImageHeader (version 12)."""
 
     def __init__(self, img: np.ndarray):
         self.b = img.tobytes()
         u = lambda fmt, off: struct.unpack_from("<" + fmt, self.b, off)  # noqa: E731
         magic, ver, hb, total, epoch = u("QIIQQ", 0)
-        assert magic == 0x3130434653303042 and ver == 11 and hb == 512 and total == len(self.b)
+        assert magic == 0x3130434653303042 and ver == 12 and hb == 512 and total == len(self.b)
         o = 32
         self.f4_off, self.f4_seed, self.f4_nb, self.f4_nh, self.f4_cnt, self.f4_first = u("QQIIII", o); o += 32
         self.f6_off, self.f6_seed, self.f6_nb, self.f6_nh, self.f6_cnt, self.f6_first = u("QQIIII", o); o += 32
@@ -45,7 +45,13 @@ class Image:
         roots = u("32I", o); o += 128
         self.acl_roots = [roots[4 * i: 4 * i + 4] for i in range(8)]
         self.lpm4_tail_off, self.lpm6_tail_off, self.lpm4_ntails, self.lpm6_ntails = u("QQII", o); o += 24
-        self.f4_slots, self.f6_slots = u("II", o)
+        self.f4_slots, self.f6_slots = u("II", o); o += 8
+        self.flow_format, self.fidx_bits = u("II", o); o += 8
+        self.fidx_off, self.fidx_seed, self.frec_off = u("QQQ", o); o += 24
+        self.fidx_nb, self.frec_units, self.frec_used, self.fidx_first = u("IIII", o); o += 16
+        self.l2x_copy_off, self.l2w_copy_off = u("QQ", o), u("QQ", o + 16); o += 32
+        self.l2x_cap, self.l2_active = u("II", o); o += 8
+        assert o == 488 and self.l2x_off == self.l2x_copy_off[self.l2_active] and self.l2w_off == self.l2w_copy_off[self.l2_active]
 
     def u32(self, off, n):
         return np.frombuffer(self.b, dtype="<u4", count=n, offset=off)
@@ -156,6 +162,57 @@ def _flow6(self, sip, dip, ports, meta20):
     return None, None
 
 
+def _flow2(self, ver, sip, dip, ports, meta20):
+    """Format 2 (sfc_common.h): flow6_hash over the full key -> two index buckets of 7 entries + overflow count ->
+    fingerprint match -> record unit(s).  Returns (result word, which bucket) or (None, None)."""
+    S = expand_seed(self.fidx_seed, 16)
+    v6 = ver == 6
+    sip, dip = list(sip) + [0] * (4 - len(sip)), list(dip) + [0] * (4 - len(dip))
+    mw = lambda a, b: (a * b) & M64  # noqa: E731
+    lo, hi = (lambda v: v & 0xFFFFFFFF), (lambda v: v >> 32)
+    meta = meta20 | (0x100000 if v6 else 0)
+    P1, P2 = mw(sip[0] ^ S[0], sip[1] ^ S[1]), mw(sip[2] ^ S[2], sip[3] ^ S[3])
+    P3, P4 = mw(dip[0] ^ S[4], dip[1] ^ S[5]), mw(dip[2] ^ S[6], dip[3] ^ S[7])
+    Q = mw(ports ^ S[8], meta ^ S[9])
+    x = lo(P1) ^ hi(P2) ^ lo(P3) ^ hi(P4) ^ hi(Q)
+    y = hi(P1) ^ lo(P2) ^ hi(P3) ^ lo(P4) ^ lo(Q)
+    F = mw(x ^ S[14], y ^ S[15])
+    B = self.fidx_bits
+    fp, mask = (lo(F) ^ hi(F)) >> B, (1 << B) - 1
+    tag = meta20 | 0x80000000 | (0x40000000 if v6 else 0)
+    buckets = []
+    for j in range(2):
+        G = mw(x ^ S[10 + 2 * j], y ^ S[11 + 2 * j])
+        buckets.append(((lo(G) ^ hi(G)) * self.fidx_nb) >> 32)
+    for j, b in enumerate(buckets):
+        if j == 1 and (b == buckets[0] or overflow == 0):  # noqa: F821  (set in the first round)
+            break
+        e = [int(v) for v in self.u32(self.fidx_off + b * 32, 8)]
+        overflow = e[7]
+        for ent in e[:7]:
+            if ent == 0 or ent >> B != fp:
+                continue
+            unit = (ent & mask) - 1
+            assert 0 <= unit < self.frec_units
+            u = [int(v) for v in self.u32(self.frec_off + unit * 32, 16)]
+            want = [tag, ports] + ([sip[0], dip[0], 0, 0] if not v6 else sip)
+            if [u[0], u[1]] + u[4:8] == want and (not v6 or u[8:12] == dip):
+                return (u[2] << 32) | u[3], j
+    return None, None
+
+
+def _flow(self, k):
+    """Look a flow key (FLOW_KEY_DTYPE record) up in whichever flow table format the image uses."""
+    ver = int(k["ip_ver"])
+    w4 = lambda b: [int.from_bytes(bytes(b[i:i + 4]), "big") for i in range(0, 16, 4)]  # noqa: E731
+    ports, meta20 = (int(k["sport"]) << 16) | int(k["dport"]), int(k["proto"]) | (int(k["vlan"]) << 8)
+    if self.flow_format == 2:
+        return self.flow2(ver, w4(k["src"]), w4(k["dst"]), ports, meta20)
+    if ver == 4:
+        return self.flow4(w4(k["src"])[0], w4(k["dst"])[0], ports, meta20)
+    return self.flow6(w4(k["src"]), w4(k["dst"]), ports, meta20)
+
+
 def _l2(self, in_port, mac):
     """Exact (in_port, dl_dst) first, then the in_port wildcard; returns the result word or None."""
     key_hi, key_lo = (in_port << 16) | int.from_bytes(mac[:2], "big"), int.from_bytes(mac[2:], "big")
@@ -177,6 +234,8 @@ def _l2(self, in_port, mac):
 
 
 Image.flow6 = _flow6
+Image.flow2 = _flow2
+Image.flow = _flow
 Image.l2 = _l2
 
 
@@ -242,6 +301,7 @@ def test_acl_forest_on_the_handmade_rules():
 @pytest.mark.parametrize("slots", [1, 2])
 def test_every_ipv4_flow_sits_in_one_of_its_buckets(slots):
     sc = Scenario(sfc.Dataplane(-1))
+    sc.dp.set_option("flow_format", 1)
     sc.dp.set_option("flow_slots", slots)
     spec = config3_spec(n_flows=20000, v6_permille=0, n_ports=8)
     install_flows(sc, spec)
@@ -260,6 +320,30 @@ def test_every_ipv4_flow_sits_in_one_of_its_buckets(slots):
         first += j == 0
     assert first / len(range(0, 20000, 7)) > 0.6  # most flows answer in their first bucket
     assert abs(img.f4_first / 20000 - first / len(range(0, 20000, 7))) < 0.05  # header statistic is honest
+
+
+def test_indexed_format_finds_every_flow_of_both_families():
+    """Format 2 (the default at this size): every flow is found through the fingerprint index, nearly all in their
+    first bucket, and keys that were never added are not found."""
+    sc = Scenario(sfc.Dataplane(-1))
+    spec = config3_spec(n_flows=30000, v6_permille=300, n_ports=8)
+    install_flows(sc, spec)
+    sc.dp.commit()
+    img = Image(sc.dp.table_export())
+    keys, acts = sfc.gen_flows(spec, 0, 31000)
+    n6 = int((keys[:30000]["ip_ver"] == 6).sum())
+    assert img.flow_format == 2 and img.f4_cnt + img.f6_cnt == 30000 and img.f6_cnt == n6
+    assert img.frec_used == 30000 + n6 and img.fidx_nb * 7 * 0.6 <= 30000 <= img.fidx_nb * 7 * 0.7
+    first = 0
+    for i in range(0, 30000, 7):
+        res, j = img.flow(keys[i])
+        assert res is not None, f"flow {i} is not where the hash says"
+        assert res & 0x0FFFFFFF == i and (res >> 28) & 0xF == consts.STAGE_FLOW and res >> 56 == int(acts[i]["action"])
+        first += j == 0
+    assert first / len(range(0, 30000, 7)) > 0.9
+    assert abs(img.fidx_first / 30000 - first / len(range(0, 30000, 7))) < 0.03
+    for i in range(30000, 31000):
+        assert img.flow(keys[i])[0] is None
 
 
 def test_forced_forests_answer_like_the_single_tree(monkeypatch):
@@ -324,10 +408,12 @@ def test_import_refuses_images_whose_indices_point_outside_their_tables():
         sfc.Dataplane(-1).table_import(good[:-256])                                               # truncated
 
 
-def test_ipv6_flows_and_l2_rules_are_where_the_kernel_will_look():
+@pytest.mark.parametrize("fmt", [1, 2])
+def test_ipv6_flows_and_l2_rules_are_where_the_kernel_will_look(fmt):
     """The two table kinds the other walks do not reach: every IPv6 flow in one of its buckets with the result the
     API was given, and the chain's L2 steering rules answering like the oracle (exact beats wildcard)."""
     sc = Scenario(sfc.Dataplane(-1))
+    sc.dp.set_option("flow_format", fmt)
     topo = sc.build_chain(8, 3)
     spec = config3_spec(n_flows=6000, v6_permille=1000, n_ports=topo["n_ports"])
     install_flows(sc, spec)
@@ -335,10 +421,8 @@ def test_ipv6_flows_and_l2_rules_are_where_the_kernel_will_look():
     img = Image(sc.dp.table_export())
     assert img.f6_cnt == 6000 and img.f4_cnt == 0
     keys, acts = sfc.gen_flows(spec, 0, 6000)
-    w4 = lambda b: [int.from_bytes(bytes(b[i:i + 4]), "big") for i in range(0, 16, 4)]  # noqa: E731
     for i in range(0, 6000, 5):
-        k = keys[i]
-        res, _ = img.flow6(w4(k["src"]), w4(k["dst"]), (int(k["sport"]) << 16) | int(k["dport"]), int(k["proto"]) | (int(k["vlan"]) << 8))
+        res, _ = img.flow(keys[i])
         assert res is not None and res & 0x0FFFFFFF == i and (res >> 28) & 0xF == consts.STAGE_FLOW and res >> 56 == int(acts[i]["action"]), i
     # L2: non-IP frames from every port towards every VF MAC and towards an unknown MAC
     import packets

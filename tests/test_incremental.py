@@ -10,13 +10,16 @@ from test_image_walk import Image
 
 
 def _flow4_probe(img, k):
-    sip, dip = int.from_bytes(bytes(k["src"][:4]), "big"), int.from_bytes(bytes(k["dst"][:4]), "big")
-    return img.flow4(sip, dip, (int(k["sport"]) << 16) | int(k["dport"]), int(k["proto"]) | (int(k["vlan"]) << 8))[0]
+    return img.flow(k)[0]
 
 
-@pytest.mark.parametrize("slots", [1, 2])
-def test_incremental_commit_patches_the_image_in_place(slots):
+FORMATS = [(1, 1), (1, 2), (2, 0)]  # (flow_format, flow_slots): both sector layouts and the indexed table
+
+
+@pytest.mark.parametrize("fmt,slots", FORMATS)
+def test_incremental_commit_patches_the_image_in_place(fmt, slots):
     dp = sfc.Dataplane(-1)
+    dp.set_option("flow_format", fmt)
     dp.set_option("flow_slots", slots)
     spec = config3_spec(n_flows=30000, v6_permille=0, n_ports=8)
     keys, acts = sfc.gen_flows(spec, 0, 30000)
@@ -31,18 +34,27 @@ def test_incremental_commit_patches_the_image_in_place(slots):
     assert first == 20000
     dp.commit()
     assert (dp.stat("full_commits"), dp.stat("incremental_commits")) == (1, 1)
-    assert 5000 <= dp.stat("patched_buckets") <= (8000 if slots == 1 else 14000)  # one slot per edit plus the cuckoo moves (more at 80 % load)
+    # sectors shipped: one slot per edit plus the cuckoo moves (more at 80 % load); the indexed table ships an index
+    # sector and a record sector per edit
+    assert 5000 <= dp.stat("patched_buckets") <= {(1, 1): 8000, (1, 2): 14000, (2, 0): 10500}[(fmt, slots)]
     assert dp.table_size == size0 and dp.table_epoch == e0 + 1
     img = Image(dp.table_export())
-    assert img.f4_cnt == 21000 and img.f4_slots == slots
+    assert img.f4_cnt == 21000 and img.flow_format == fmt and (fmt == 2 or img.f4_slots == slots)
     for i in list(range(1, 4000, 2)) + list(range(4000, 23000, 37)):  # alive
         r = _flow4_probe(img, keys[i])
         assert r is not None and r & 0x0FFFFFFF == i, i
     for i in range(0, 4000, 2):  # deleted
         assert _flow4_probe(img, keys[i]) is None, i
-    # anything that is not a flow edit forces the rebuild path
+    # L2 steering rules do not rebuild either: they go into the idle copy of the L2 tables
     p = dp.port_add("x")
     dp.l2_rule_add(p, p)
+    dp.commit()
+    assert (dp.stat("full_commits"), dp.stat("incremental_commits")) == (1, 2)
+    img2 = Image(dp.table_export())
+    assert img2.l2_active == 1 - img.l2_active and img2.l2w_cnt == img.l2w_cnt + 1
+    assert img2.l2(p, bytes(6)) >> 56 == consts.ACT_FORWARD and img.l2(p, bytes(6)) is None
+    # anything else (LPM, ACL, the chain) forces the rebuild path
+    dp.lpm_add(4, bytes([10, 0, 0, 0]), 8, p)
     dp.commit()
     assert dp.stat("full_commits") == 2
 
@@ -82,10 +94,11 @@ def test_flow_index_survives_heavy_delete_churn():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("slots", [1, 2])
-def test_flow_churn_between_launches_on_the_gpu(torch_cuda, slots):
+@pytest.mark.parametrize("fmt,slots", FORMATS)
+def test_flow_churn_between_launches_on_the_gpu(torch_cuda, fmt, slots):
     torch = torch_cuda
     dp = sfc.Dataplane(0)
+    dp.set_option("flow_format", fmt)
     dp.set_option("flow_slots", slots)
     sc = Scenario(dp)
     topo = sc.build_chain(8, 2)
@@ -120,7 +133,7 @@ def test_flow_churn_between_launches_on_the_gpu(torch_cuda, slots):
         want = sc.orc.classify(hdr, ports, threads=8)
         bad = int((got != want).sum())
         assert bad == 0, f"round {rnd}: {bad} results differ after incremental commit"
-    if slots == 1:
+    if slots != 2:
         assert dp.stat("incremental_commits") == 6 and dp.stat("full_commits") == 1
     else:  # built at 80 % load: the net growth of 1000 flows a round forces a rebuild along the way
         assert dp.stat("incremental_commits") + dp.stat("full_commits") == 7 and dp.stat("incremental_commits") >= 4

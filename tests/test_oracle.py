@@ -98,3 +98,35 @@ def test_l2_delete_is_loose_like_ovs_del_flows():
     assert sfc.result_fields(sc.orc.classify(frame, p))[3][0] == consts.STAGE_L2_EXACT
     sc.l2_del(inp, None)
     assert sc.orc.classify(frame, p)[0] == consts.RESULT_MISS
+
+
+def test_the_two_writings_of_the_workload_agree_byte_for_byte():
+    """oracle/workload.cpp and the product's generator (csrc/gen.h) implement one specification twice; flows,
+    packets, prefixes, MACs and ACL rules must come out identical for every traffic mix the configs use."""
+    from common import OracleGen, config2_spec, config3_spec, config4_spec
+
+    specs = [config2_spec(), config3_spec(n_flows=50000, n_ports=17), config3_spec(n_flows=(1 << 20) + 12345, n_ports=9, zipf=1),
+             config4_spec(n_pfx4=3000, n_pfx6=900, n_acl=300), config3_spec(n_flows=777, v6_permille=1000, vlan_permille=1000, zipf=0)]
+    for spec in specs:
+        nf = min(int(spec["n_flows"][0]), 20000)
+        if nf:
+            k1, a1 = sfc.gen_flows(spec, 3, nf - 3)
+            k2, a2 = OracleGen.flows(spec, 3, nf - 3)
+            assert k1.tobytes() == k2.tobytes() and a1.tobytes() == a2.tobytes()
+        h1, p1 = sfc.gen_packets_host(spec, 1000, 30000)
+        h2, p2 = OracleGen.packets(spec, 1000, 30000)
+        assert np.array_equal(p1, p2)
+        assert np.array_equal(h1, h2), f"first differing packet: {int(np.nonzero((h1 != h2).any(axis=1))[0][0])}"
+        for af, n in ((4, int(spec["n_pfx4"][0])), (6, int(spec["n_pfx6"][0]))):
+            mine = OracleGen.prefixes(spec, af, min(n, 500))
+            theirs = []
+            for j in range(min(n, 500)):
+                import ctypes as C
+                buf, ln, port = C.create_string_buffer(16), C.c_int(), C.c_uint16()
+                sfc.capi.lib.sfc_gen_prefix(spec.ctypes.data, af, j, C.cast(buf, C.c_void_p), C.byref(ln), C.byref(port))
+                theirs.append((buf.raw[: 4 if af == 4 else 16], ln.value, port.value))
+            assert mine == theirs
+        na = int(spec["n_acl"][0])
+        if na:
+            assert OracleGen.acl_rules(spec, na).tobytes() == sfc.gen_acl_rules(spec, na).tobytes()
+    assert all(OracleGen.mac(i) == sfc.gen_mac(i) for i in (0, 1, 7, 255, 256, 70000))
