@@ -308,6 +308,13 @@ __device__ __forceinline__ bool flow4_lookup(const DevTables& T, const Key& k, u
             s[4] = t[4];
             s[5] = t[5];
         }
+    } else if (T.flow4_mode & kProbeL1) {  // lazy, probes may stay in L1: skewed traffic keeps its hot sectors there
+        ldg256_l1(p0, s);
+        hit = flow4_match(s, k, tag);
+        if (!hit) {
+            ldg256_l1(p1, s);
+            hit = flow4_match(s, k, tag);
+        }
     } else {
         ldg256(p0, s);
         hit = flow4_match(s, k, tag);

@@ -117,7 +117,6 @@ constexpr int kFidxEntries = 7;
 constexpr int kFidxBucketWords = 8;
 constexpr int kFrecUnitWords = 8;
 constexpr uint32_t kFlowFormatSector = 1, kFlowFormatIndexed = 2;
-constexpr uint64_t kFlowIndexedMaxUnits = 3ull << 20;  // format chosen by size: up to ~100 MB of records use the index
 SFC_HD uint32_t flow_fp(uint32_t x, uint32_t y, const uint32_t* T) {  // T = the six bucket-choice seed words
     uint64_t F = mul_wide(x ^ T[4], y ^ T[5]);
     return (uint32_t)F ^ (uint32_t)(F >> 32);

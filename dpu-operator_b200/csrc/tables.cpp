@@ -1059,8 +1059,9 @@ bool build_image(const RuleStore& rs, uint64_t epoch, std::vector<uint8_t>& imag
     // and nothing else, which is what counts once the records cannot stay in L2 anyway.
     const uint64_t units_needed = (uint64_t)f4.size() + 2ull * f6.size();
     uint32_t format = (uint32_t)rs.flow_format;
-    if (format != kFlowFormatSector && format != kFlowFormatIndexed)
-        format = units_needed <= kFlowIndexedMaxUnits ? kFlowFormatIndexed : kFlowFormatSector;
+    // measured on B200 (profiles/r02_experiments.md): the sector tables are faster at every size, so they are
+    // what "by size" picks; the indexed table is for images that must be small
+    if (format != kFlowFormatSector && format != kFlowFormatIndexed) format = kFlowFormatSector;
     if (format == kFlowFormatIndexed && units_needed + units_needed / 8 + 8192 >= (1ull << 27)) format = kFlowFormatSector;
     H.flow_format = format;
     if (format == kFlowFormatIndexed) {

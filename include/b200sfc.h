@@ -145,8 +145,21 @@ const char* sfc_last_error(const sfc_handle* h);
 /* Library version string "b200sfc <major>.<minor>" and the image format number. */
 const char* sfc_version(void);
 
-/* Tuning knobs, set before sfc_commit.  Known names: "flow_load_pct" (10..90, table load factor
- * target), "flow_hashes" (2 or 3).  No reference counterpart (the reference has no table). */
+/* Tuning knobs.  No reference counterpart (the reference has no table).  Table-shape options take effect at the
+ * next sfc_commit, which then rebuilds the image:
+ *   "flow_format"     0 by size (default; picks 1), 1 one-sector cuckoo tables per address family, 2 fingerprint
+ *                     index + dense records (half the memory, slower: profiles/r02_experiments.md)
+ *   "flow_load_pct"   0 = the format's default (40 / 65), else 5..90: load factor the flow tables are built at
+ *   "flow_hashes"     2 (default) or 3 bucket choices per flow (format 1)
+ *   "flow_slots"      0 / 1 one slot per bucket (default), 2 dense two-slot buckets (format 1)
+ * Launch-policy options take effect at once:
+ *   "flow_probe_mode" -1 by table size (default); bit 0 = issue both probes at once, bit 1 = probes may stay in L1
+ *   "low_regs"        -1 by table size (default), 0 / 1: run the 40-register kernels (five CTAs per SM)
+ * sfc_classify_host pipeline:
+ *   "host_chunk"      packets per chunk (1024 .. 262144, default 262144)
+ *   "host_bufs"       chunks in flight (2 .. 4, default 2)
+ *   "host_timing"     1 = record kernel time per chunk for sfc_last_kernel_ms (costs ~1 %)
+ * Unknown names return -ENOENT.  (The experiment build, `make tune`, adds tune_* options; they are not part of this ABI.) */
 int sfc_set_option(sfc_handle* h, const char* name, long value);
 
 /* ---------------------------------------------------------------- port registry --------- */

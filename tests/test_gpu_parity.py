@@ -1,5 +1,7 @@
 """GPU parity: the CUDA path, called through the C ABI, must be bit-exact against the CPU oracle
 on the same inputs (integer work: no tolerance)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -132,10 +134,10 @@ def test_config4_lpm_acl(torch_cuda):
     spec = config4_spec()
     install_lpm_acl(sc, spec)
     dp.commit()
-    n = 1 << 18  # the oracle's ACL is a linear scan of 1024 rules per packet
+    n = 1 << 22  # the oracle's ACL is a linear scan of 1024 rules per packet: all host threads
     hdr, ports = gen_dev(torch_cuda, dp, spec, 0, n)
     got = classify_dev(torch_cuda, dp, hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16))
-    want = sc.orc.classify(hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), threads=8)
+    want = sc.orc.classify(hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), threads=os.cpu_count() or 8)
     assert_same(got, want, hdr.cpu().numpy())
     stage = sfc.result_fields(got)[3]
     for s in (consts.STAGE_ACL, consts.STAGE_LPM4, consts.STAGE_LPM6, consts.STAGE_MISS):
@@ -516,3 +518,93 @@ def test_launches_survive_cuda_graph_capture_and_replay(torch_cuda):
         g.replay()
         t.cuda.synchronize()
         assert t.equal(res, want)
+
+
+def test_indexed_flow_format_on_the_gpu(torch_cuda):
+    """Option flow_format = 2 (fingerprint index + dense records, one code path for IPv4 and IPv6): same answers and
+    counters as the oracle on mixed traffic, in an image about half the size."""
+    sizes = {}
+    for fmt in (1, 2):
+        dp = sfc.Dataplane(0)
+        dp.set_option("flow_format", fmt)
+        sc = Scenario(dp)
+        topo = sc.build_chain(8, 3)
+        spec = config3_spec(n_flows=300000, n_ports=topo["n_ports"])
+        install_flows(sc, spec)
+        dp.commit()
+        sizes[fmt] = dp.table_size
+        hdr, ports = gen_dev(torch_cuda, dp, spec, 0, 1 << 19)
+        got = classify_dev(torch_cuda, dp, hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), consts.F_COUNTERS)
+        want, cnt = sc.orc.classify(hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), threads=8, counters=True)
+        assert_same(got, want, hdr.cpu().numpy())
+        assert np.array_equal(dp.counters_read(), cnt)
+        assert (sfc.result_fields(got)[3] == consts.STAGE_FLOW).mean() > 0.5
+    assert sizes[2] < 0.65 * sizes[1]
+
+
+def test_config5_16m_flows_against_the_oracle(torch_cuda):
+    """configs[4] table at full size — 16 Mi flows (20 % IPv6) resident, Zipf traffic, 4-NF chain, counters on —
+    compared word for word with the oracle holding the same 16 Mi flows, on 2^22 packets; the flows go into the
+    oracle from ITS generator (oracle/workload.cpp), into the library from the product's."""
+    from common import OracleGen
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    topo = sc.build_chain(8, 4)
+    nf = 1 << 24
+    spec = config3_spec(n_flows=nf, n_ports=topo["n_ports"])
+    for first in range(0, nf, 1 << 20):
+        assert dp.flow_add_bulk(*sfc.gen_flows(spec, first, 1 << 20)) == first
+        sc.orc.flow_add(*OracleGen.flows(spec, first, 1 << 20), first)
+    dp.commit()
+    n = 1 << 22
+    hdr, ports = gen_dev(torch_cuda, dp, spec, 5 << 22, n)
+    got = classify_dev(torch_cuda, dp, hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), consts.F_COUNTERS)
+    oh, op = OracleGen.packets(spec, 5 << 22, n)
+    want, cnt = sc.orc.classify(oh, op, threads=os.cpu_count() or 8, counters=True)
+    assert_same(got, want, oh)
+    assert np.array_equal(dp.counters_read(), cnt)
+    stage = sfc.result_fields(got)[3]
+    assert (stage == consts.STAGE_FLOW).mean() > 0.8 and (stage == consts.STAGE_MISS).sum() > 0
+
+
+@pytest.mark.parametrize("with_acl,low_regs", [(True, -1), (False, 0), (False, 1)])
+def test_every_kernel_variant_is_stable_under_overlapped_launches(torch_cuda, with_acl, low_regs):
+    """Race guard for the variants test_repeated_launches_are_stable does not reach: the one-stage ACL kernels, the
+    40-register kernels, the multi-batch kernels and the counters variants, all under overlapped (programmatic
+    dependent) launches over rotating buffers; every launch's full result array is compared with the oracle's."""
+    torch = torch_cuda
+    F = consts
+    n, pool, iters = 1 << 18, 6, 4
+    dp = sfc.Dataplane(0)
+    sc = Scenario(dp)
+    dp.set_option("low_regs", low_regs)
+    topo = sc.build_chain(8, 3)
+    spec = config3_spec(n_flows=200000, n_ports=topo["n_ports"] + 2, n_pfx4=5000, n_pfx6=2000, lpm_permille=600,
+                        n_acl=200 if with_acl else 0, hit_permille=700)
+    install_flows(sc, spec)
+    install_lpm_acl(sc, spec)
+    dp.commit()
+    st = torch.cuda.current_stream().cuda_stream
+    hdr = torch.empty((pool, n, 64), dtype=torch.uint8, device="cuda")
+    ports = torch.empty((pool, n), dtype=torch.int16, device="cuda")
+    res = torch.zeros((pool, n), dtype=torch.int64, device="cuda")
+    for b in range(pool):
+        dp.gen_packets(spec, b * n, n, hdr[b].data_ptr(), ports[b].data_ptr(), st)
+    torch.cuda.synchronize()
+    want = torch.stack([torch.from_numpy(sc.orc.classify(hdr[b].cpu().numpy(), ports[b].cpu().numpy().view(np.uint16),
+                                                         threads=os.cpu_count() or 8).view(np.int64)) for b in range(pool)]).cuda()
+    cuts = [0, 4096, 4096 + 255, 70000, 70000 + 513, 200000, n]
+    for mode in ("classify", "classify+counters", "batches", "batches+counters"):
+        flags = F.F_OVERLAP | (F.F_COUNTERS if "counters" in mode else 0)
+        for it in range(iters):
+            res.zero_()
+            for i in range(pool * 6):
+                b = i % pool
+                if mode.startswith("batches"):
+                    dp.classify_batches([(hdr[b].data_ptr() + a * 64, ports[b].data_ptr() + a * 2, res[b].data_ptr() + a * 8, e - a)
+                                         for a, e in zip(cuts, cuts[1:])], flags, st)
+                else:
+                    dp.classify(hdr[b].data_ptr(), ports[b].data_ptr(), res[b].data_ptr(), n, flags, st)
+            torch.cuda.synchronize()
+            bad = int((res != want).sum())
+            assert bad == 0, f"{mode}, iteration {it}: {bad} results differ from the oracle"

@@ -323,9 +323,10 @@ def test_every_ipv4_flow_sits_in_one_of_its_buckets(slots):
 
 
 def test_indexed_format_finds_every_flow_of_both_families():
-    """Format 2 (the default at this size): every flow is found through the fingerprint index, nearly all in their
+    """Format 2 (option flow_format): every flow is found through the fingerprint index, nearly all in their
     first bucket, and keys that were never added are not found."""
     sc = Scenario(sfc.Dataplane(-1))
+    sc.dp.set_option("flow_format", 2)
     spec = config3_spec(n_flows=30000, v6_permille=300, n_ports=8)
     install_flows(sc, spec)
     sc.dp.commit()

@@ -5,31 +5,31 @@ thread living inside a fixed memory budget, a shim inside a process whose device
 to another runtime, a polling loop that must stay off the driver's allocation locks.  For them the
 library keeps the classify kernel's scratch (its tile tickets) and the table image in a fixed
 array compiled into the library, and takes no handle.  This file checks, through the C ABI and on
-two calls in a row, that the results are bit-identical to the ordinary handle-based entry point,
-that the shared array is re-armed correctly between calls, that free device memory does not move
-across a call, and that an image larger than the fixed area is refused with a message that says so.
+two calls in a row, that the results are bit-identical to the ordinary handle-based entry point AND
+to the CPU oracle — with and without ACL rules in the image, because the two cases run different
+kernels — that the shared array is re-armed correctly between calls, that free device memory does
+not move across a call, and that an image larger than the fixed area is refused with a message that
+says so.
 
 It is named so that pytest collects it last: if it fails under -x every other test has already run.
 """
 import numpy as np
 import pytest
 
-from common import Scenario, config3_spec, install_flows, sfc
+from common import Scenario, config3_spec, install_flows, install_lpm_acl, sfc
 
 pytestmark = pytest.mark.gpu
 
 
-def _scenario():
+def _scenario(n_acl):
     dp = sfc.Dataplane(0)
     sc = Scenario(dp)
     topo = sc.build_chain(8, 2)
-    spec = config3_spec(n_flows=20000, n_ports=topo["n_ports"] + 2, n_pfx4=500, n_pfx6=100, lpm_permille=600)
+    spec = config3_spec(n_flows=20000, n_ports=topo["n_ports"] + 2, n_pfx4=500, n_pfx6=100, lpm_permille=600, n_acl=n_acl)
     install_flows(sc, spec)
-    for af, n in ((4, 500), (6, 100)):
-        for p, ln, port in sfc.gen_prefixes(spec, af, n):
-            sc.lpm_add(af, p, ln, port)
+    install_lpm_acl(sc, spec)  # n_acl == 0: prefixes only
     dp.commit()
-    return dp, spec
+    return dp, sc, spec
 
 
 def _batch(torch, dp, spec, first, n):
@@ -40,9 +40,10 @@ def _batch(torch, dp, spec, first, n):
     return hdr, ports
 
 
-def test_static_entry_point_matches_the_handle_entry_point_twice(torch_cuda):
+@pytest.mark.parametrize("n_acl", [0, 120])
+def test_static_entry_point_matches_the_handle_entry_point_twice(torch_cuda, n_acl):
     torch = torch_cuda
-    dp, spec = _scenario()
+    dp, sc, spec = _scenario(n_acl)
     image = dp.table_export()  # host copy of the committed image: the caller's input
     assert image.size <= sfc.STATIC_AREA_BYTES - 256
     st = torch.cuda.current_stream().cuda_stream
@@ -53,7 +54,10 @@ def test_static_entry_point_matches_the_handle_entry_point_twice(torch_cuda):
         dp.classify(hdr.data_ptr(), ports.data_ptr(), res.data_ptr(), ports.numel(), 0, st)
         torch.cuda.synchronize()
         want.append(res)
-    assert len({int(x) for x in sfc.result_fields(want[0].cpu().numpy().view(np.uint64))[3]}) >= 5  # a real mix of stages
+        # the oracle's answer for the same packets: the static path below is thereby held to the oracle as well
+        orc = sc.orc.classify(hdr.cpu().numpy(), ports.cpu().numpy().view(np.uint16), threads=8)
+        assert np.array_equal(res.cpu().numpy().view(np.uint64), orc)
+    assert len({int(x) for x in sfc.result_fields(want[0].cpu().numpy().view(np.uint64))[3]}) >= (6 if n_acl else 5)  # a real mix of stages
 
     got = [torch.full((p.numel(),), -1, dtype=torch.int64, device="cuda") for _, p in batches]
     # call 1 carries the image; call 2 reuses what call 1 left in the static array
