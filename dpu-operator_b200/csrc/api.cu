@@ -596,7 +596,14 @@ int sfc_port_del(sfc_handle* h, const char* name) {
     if (!h || !name) return -EINVAL;
     auto it = h->rs.port_by_name.find(name);
     if (it == h->rs.port_by_name.end()) return fail(h, -ENOENT, "sfc_port_del: no port named '%s'", name);
-    h->rs.port_names[it->second].clear();
+    // The id goes back into the pool (sfc_port_add hands out the lowest free one), so steering rules that name
+    // it must not outlive it: with OVS a flow that names a removed port stops matching; here it is dropped.
+    const uint16_t id = it->second;
+    auto& v = h->rs.l2;
+    const size_t before = v.size();
+    v.erase(std::remove_if(v.begin(), v.end(), [&](const L2Rule& e) { return e.in_port == id || e.out_port == id; }), v.end());
+    if (v.size() != before) h->rs.l2_dirty = true;
+    h->rs.port_names[id].clear();
     h->rs.port_by_name.erase(it);
     return 0;
 }

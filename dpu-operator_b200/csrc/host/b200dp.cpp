@@ -30,6 +30,21 @@ int B200DP::fail(int rc) {
     return rc;
 }
 
+int B200DP::commit() {
+    if (batch_depth_ > 0) {
+        commit_pending_ = true;
+        return 0;
+    }
+    return sfc_commit(h_);
+}
+
+int B200DP::EndBatch() {
+    if (batch_depth_ > 0 && --batch_depth_ > 0) return 0;
+    if (!commit_pending_ || !h_) return 0;
+    commit_pending_ = false;
+    return fail(sfc_commit(h_));
+}
+
 // ovs-vsctl --may-exist add-br <bridge> + add the RPM (wire) port — ovs-dp/ovsdp.go:71-102
 int B200DP::InitDataPlane(const std::string& bridgeName) {
     if (h_) return 0;  // --may-exist
@@ -48,14 +63,17 @@ int B200DP::InitDataPlane(const std::string& bridgeName) {
 int B200DP::AddPortToDataPlane(const std::string&, const std::string& portName, const std::string&, bool) {
     if (!h_) return fail(-ENODEV);
     int rc = sfc_port_add(h_, portName.c_str(), nullptr);
-    return rc ? fail(rc) : fail(sfc_commit(h_));
+    return rc ? fail(rc) : fail(commit());
 }
 
 // ovs-vsctl del-port <bridge> <port> — ovs-dp/ovsdp.go:58-62
 int B200DP::DeletePortFromDataPlane(const std::string&, const std::string& portName) {
     if (!h_) return fail(-ENODEV);
-    int rc = sfc_port_del(h_, portName.c_str());
-    return rc ? fail(rc) : fail(sfc_commit(h_));
+    int rc = sfc_port_del(h_, portName.c_str());  // also drops the steering rules that name the port
+    if (rc) return fail(rc);
+    flows_.erase(std::remove_if(flows_.begin(), flows_.end(), [&](const Flow& f) { return f.in == portName || f.out == portName; }),
+                 flows_.end());
+    return fail(commit());
 }
 
 // ovs-vsctl list-ports <bridge> — ovs-dp/ovsdp.go:104-112
@@ -106,7 +124,7 @@ int B200DP::AddFlowRuleToDataPlane(const std::string&, const std::string& inPort
     auto it = std::find_if(flows_.begin(), flows_.end(), same);
     if (it != flows_.end()) it->out = outPort;
     else flows_.push_back(Flow{inPort, outPort, dstMac});
-    return fail(sfc_commit(h_));
+    return fail(commit());
 }
 
 // ovs-ofctl del-flows <bridge> in_port=S[,dl_dst=M] — ovs-dp/ovsdp.go:143-162 (a loose match)
@@ -128,7 +146,7 @@ int B200DP::DeleteFlowRuleFromDataPlane(const std::string&, const std::string& i
     flows_.erase(std::remove_if(flows_.begin(), flows_.end(),
                                 [&](const Flow& f) { return f.in == inPort && (dstMac.empty() || f.mac == dstMac); }),
                  flows_.end());
-    return fail(sfc_commit(h_));
+    return fail(commit());
 }
 
 std::vector<std::string> B200DP::FlowDump() const {

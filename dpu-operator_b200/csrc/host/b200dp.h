@@ -32,6 +32,13 @@ class B200DP {
     int DeleteFlowRuleFromDataPlane(const std::string& bridgeName, const std::string& inPort, const std::string& outPort,
                                     const std::string& dstMac);
 
+    // One RPC of the vendor plugin programs several ports and rules (CreateBridgePort: one port + three rules,
+    // marvell/main.go:347-421).  Between BeginBatch and EndBatch the methods above only stage; EndBatch makes
+    // everything staged visible with ONE table commit.  Outside a batch every method commits by itself, like
+    // one ovs-vsctl / ovs-ofctl invocation of the reference backend.
+    void BeginBatch() { ++batch_depth_; }
+    int EndBatch();
+
     const std::string& LastError() const { return err_; }
     sfc_handle* handle() const { return h_; }
     const std::string& rpm_port() const { return rpm_port_; }
@@ -44,6 +51,9 @@ class B200DP {
         std::string in, out, mac;
     };
     int fail(int rc);
+    int commit();
+    int batch_depth_ = 0;
+    bool commit_pending_ = false;
     int device_;
     std::string rpm_port_, bridge_, err_;
     sfc_handle* h_ = nullptr;

@@ -7,6 +7,26 @@
 
 namespace sfc {
 
+namespace {
+// Everything one RPC programs becomes visible with one table commit (B200DP::BeginBatch / EndBatch).
+struct RpcBatch {
+    B200DP& dp;
+    explicit RpcBatch(B200DP& d) : dp(d) { dp.BeginBatch(); }
+    // rc = what the RPC body returned (its error text is already in place); a failing commit only shows
+    // when the body itself succeeded
+    int end(int rc, bool* commit_failed) {
+        const int rc2 = dp.EndBatch();
+        done = true;
+        *commit_failed = !rc && rc2;
+        return rc ? rc : rc2;
+    }
+    ~RpcBatch() {
+        if (!done) dp.EndBatch();
+    }
+    bool done = false;
+};
+}  // namespace
+
 int MrvlVsp::fail(int rc) {
     if (rc) err_ = dp_.LastError();
     return rc;
@@ -35,6 +55,12 @@ int MrvlVsp::getVFDetails(const std::string& name, std::string* vfName) {
 
 // CreateBridgePort (:347-421)
 int MrvlVsp::CreateBridgePort(const std::string& name, const uint8_t mac[6], std::string* out_name) {
+    RpcBatch batch(dp_);
+    bool cf;
+    const int rc = batch.end(createBridgePort(name, mac, out_name), &cf);
+    return cf ? fail(rc) : rc;
+}
+int MrvlVsp::createBridgePort(const std::string& name, const uint8_t mac[6], std::string* out_name) {
     std::string vfName;
     int rc = getVFDetails(name, &vfName);
     if (rc) return rc;
@@ -53,6 +79,12 @@ int MrvlVsp::CreateBridgePort(const std::string& name, const uint8_t mac[6], std
 
 // DeleteBridgePort (:425-486)
 int MrvlVsp::DeleteBridgePort(const std::string& name) {
+    RpcBatch batch(dp_);
+    bool cf;
+    const int rc = batch.end(deleteBridgePort(name), &cf);
+    return cf ? fail(rc) : rc;
+}
+int MrvlVsp::deleteBridgePort(const std::string& name) {
     std::string vfName;
     int rc = getVFDetails(name, &vfName);
     if (rc) return rc;
@@ -81,8 +113,11 @@ int MrvlVsp::DeleteBridgePort(const std::string& name) {
 // CreateNetworkFunction (:490-497): MACs of the NF-side interfaces -> dataplane-side names
 int MrvlVsp::CreateNetworkFunction(const std::string& input, const std::string& output) {
     is_nf_ = true;
+    RpcBatch batch(dp_);
     // an unknown MAC yields the zero value "" in Go (:493-494) and the add-port then fails
-    return AddNetworkFunction(device_store_[input], device_store_[output], kNfName);
+    bool cf;
+    const int rc = batch.end(AddNetworkFunction(device_store_[input], device_store_[output], kNfName), &cf);
+    return cf ? fail(rc) : rc;
 }
 
 // AddNetworkFunction (:501-563)
@@ -115,7 +150,10 @@ int MrvlVsp::AddNetworkFunction(const std::string& inp, const std::string& out, 
 // DeleteNetworkFunction (:565-572)
 int MrvlVsp::DeleteNetworkFunction(const std::string& input, const std::string& output) {
     is_nf_ = false;
-    return DeleteNetworkFunctionPort(device_store_[input], device_store_[output], kNfName);
+    RpcBatch batch(dp_);
+    bool cf;
+    const int rc = batch.end(DeleteNetworkFunctionPort(device_store_[input], device_store_[output], kNfName), &cf);
+    return cf ? fail(rc) : rc;
 }
 
 // DeleteNetworkFunctionPort (:575-618)

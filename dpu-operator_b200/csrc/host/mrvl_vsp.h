@@ -49,6 +49,8 @@ class MrvlVsp {
         std::string inpPort, outPort;
     };
     int fail(int rc);
+    int createBridgePort(const std::string& name, const uint8_t mac[6], std::string* out_name);  // RPC bodies: one commit per RPC around them
+    int deleteBridgePort(const std::string& name);
     int getVFDetails(const std::string& bridgePortName, std::string* vfName);
     int AddNetworkFunction(const std::string& inp, const std::string& out, const std::string& nfName);
     int DeleteNetworkFunctionPort(const std::string& inp, const std::string& out, const std::string& nfName);

@@ -170,8 +170,9 @@ int sfc_set_option(sfc_handle* h, const char* name, long value);
  * marvell/main.go:55, ovs-dp/ovsdp.go:40-55. */
 int sfc_port_add(sfc_handle* h, const char* name, uint16_t* port_id);
 
-/* Remove a port; -ENOENT if unknown.  Rules naming the port are NOT removed (OVS keeps flows
- * that name a deleted ofport too); they simply stop matching once the id is gone from traffic.
+/* Remove a port; -ENOENT if unknown.  The L2 steering rules that name the port (as in_port or out_port) are
+ * removed with it: with OVS a flow that names a deleted port stops matching, and here the id is handed out again
+ * by the next sfc_port_add, so a rule left behind would steer the NEW port's traffic.  Takes effect at sfc_commit.
  * Replaces: mrvldp.DeletePortFromDataPlane — marvell/main.go:56, ovs-dp/ovsdp.go:58-62. */
 int sfc_port_del(sfc_handle* h, const char* name);
 

@@ -115,3 +115,29 @@ int main(void) {
                     "-L", libdir, "-lb200sfc", f"-Wl,-rpath,{libdir}"], check=True)
     out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.strip().split("|")
     assert out[0].startswith("b200sfc") and int(out[1]) > 512 and "offline" in out[2]
+
+
+def test_a_deleted_port_takes_its_steering_rules_with_it():
+    """Port ids are recycled (lowest free id first).  A port added after a delete must not inherit the old
+    port's rules: sfc_port_del drops the L2 rules naming the id (OVS: flows naming a removed port stop matching)."""
+    import numpy as np
+    from common import Scenario, sfc
+    from test_image_walk import Image
+
+    sc = Scenario(sfc.Dataplane(-1))
+    dp = sc.dp
+    a, b, c = dp.port_add("a"), dp.port_add("b"), dp.port_add("c")
+    mac = bytes.fromhex("020000000001")
+    dp.l2_rule_add(b, c)          # in_port = b
+    dp.l2_rule_add(a, b, mac)     # out_port = b
+    dp.l2_rule_add(a, c)          # does not name b
+    dp.commit()
+    img = Image(dp.table_export())
+    assert img.l2(b, bytes(6)) is not None and img.l2(a, mac) & 0xFFFF == b
+    dp.port_del("b")
+    assert dp.port_add("new") == b  # the id is recycled
+    dp.commit()
+    img = Image(dp.table_export())
+    assert img.l2(b, bytes(6)) is None, "the new port inherited the deleted port's wildcard rule"
+    assert img.l2(a, mac) & 0xFFFF == c and (img.l2(a, mac) >> 28) & 0xF == sfc.consts.STAGE_L2_WILD  # the MAC rule towards b is gone
+    assert dp.stat("full_commits") == 1  # L2 edits go into the idle copy, no rebuild

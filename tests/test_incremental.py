@@ -139,3 +139,106 @@ def test_flow_churn_between_launches_on_the_gpu(torch_cuda, fmt, slots):
         assert dp.stat("incremental_commits") + dp.stat("full_commits") == 7 and dp.stat("incremental_commits") >= 4
     hits = (sfc.result_fields(got)[3] == consts.STAGE_FLOW).mean()
     assert 0.3 < hits < 0.9
+
+
+def _oracle_from_dump(v):
+    """An oracle holding exactly the steering rules the VSP mirror has programmed (rule ids = dump order)."""
+    dp, orc = v.dataplane, Oracle()
+    mac = lambda s: bytes(int(x, 16) for x in s.split(":"))  # noqa: E731
+    for rid, line in enumerate(v.flow_dump()):
+        f = dict(kv.split("=", 1) for kv in line.split(",") if "=" in kv)
+        inp = dp.port_lookup(f["in_port"])
+        out = inp if line.endswith("actions=in_port") else dp.port_lookup(line.rsplit("output:", 1)[1])
+        orc.l2_add(inp, out, mac(f["dl_dst"]) if "dl_dst" in f else None, int(f.get("priority", consts.PRIO_MAC)), rid)
+    return orc
+
+
+@pytest.mark.gpu
+def test_bridge_port_churn_while_another_thread_classifies(torch_cuda):
+    """The reference's real churn (marvell/main.go:347-486): with 1 Mi flows resident, one thread adds and deletes
+    a bridge port 1000 times through the VSP mirror — one port and three steering rules per RPC, ONE table commit per
+    RPC, never a rebuild — while another thread classifies without pause on its own stream.  Every launch must equal
+    the oracle of the rule set before or after the RPC in flight (a launch sees one epoch, never a mixture), and a
+    CreateBridgePort must stay under a millisecond."""
+    import threading
+    import time
+
+    torch = torch_cuda
+    v = sfc.VspServer(0, "rpm0")
+    nf_macs = ["02:00:00:00:aa:01", "02:00:00:00:aa:02"]
+    for m, ifc in zip(nf_macs, ("nfdp0", "nfdp1")):
+        v.add_nf_device(m, ifc)
+    v.Init(True)
+    vf_mac = lambda i: bytes([0x00, i, 0x00, 0x00, 0x03, 0x14])  # noqa: E731
+    for i in range(4):
+        v.CreateBridgePort(f"host0-{i}", vf_mac(i))
+    v.CreateNetworkFunction(*nf_macs)
+    dp = v.dataplane
+    spec = config3_spec(n_flows=1 << 20, n_ports=12, hit_permille=300, nonip_permille=400, n_macs=6)
+    for first in range(0, 1 << 20, 1 << 18):
+        dp.flow_add_bulk(*sfc.gen_flows(spec, first, 1 << 18))
+    dp.commit()
+    full0 = dp.stat("full_commits")
+    # the two rule sets the churn alternates between
+    orc_a = _oracle_from_dump(v)
+    v.CreateBridgePort("host0-4", vf_mac(4))
+    orc_b = _oracle_from_dump(v)
+    v.DeleteBridgePort("host0-4")
+    keys, acts = sfc.gen_flows(spec, 0, 1 << 20)
+    for o in (orc_a, orc_b):
+        o.flow_add(keys, acts, 0)
+    n = 1 << 16
+    hdr, ports = sfc.gen_packets_host(spec, 0, n)
+    # rule ids grow with every add: compare decisions (action, next NF, port, stage), not the id of an L2 rule
+    def decisions(r):
+        r = np.asarray(r, dtype=np.uint64)
+        l2 = ((r >> np.uint64(28)) & np.uint64(0xF) == consts.STAGE_L2_EXACT) | ((r >> np.uint64(28)) & np.uint64(0xF) == consts.STAGE_L2_WILD)
+        return np.where(l2, r & ~np.uint64(0x0FFFFFFF), r)
+    want_a, want_b = decisions(orc_a.classify(hdr, ports, threads=8)), decisions(orc_b.classify(hdr, ports, threads=8))
+    assert (want_a != want_b).sum() > 100  # the port under churn carries traffic
+
+    stop, errors, launches = threading.Event(), [], [0, 0, 0]
+
+    def classify_loop():
+        try:
+            torch.cuda.set_device(0)
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                d_hdr = torch.from_numpy(hdr).cuda()
+                d_ports = torch.from_numpy(ports.view(np.int16)).cuda()
+                res = torch.zeros(n, dtype=torch.int64, device="cuda")
+                while not stop.is_set():
+                    dp.classify(d_hdr.data_ptr(), d_ports.data_ptr(), res.data_ptr(), n, 0, s.cuda_stream)
+                    s.synchronize()
+                    got = decisions(res.cpu().numpy().view(np.uint64))
+                    a, b = bool(np.array_equal(got, want_a)), bool(np.array_equal(got, want_b))
+                    launches[0] += 1
+                    launches[1] += a
+                    launches[2] += b
+                    if not (a or b):
+                        errors.append(f"launch {launches[0]}: {int((got != want_a).sum())} words differ from epoch A, "
+                                      f"{int((got != want_b).sum())} from epoch B")
+                        return
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    t = threading.Thread(target=classify_loop)
+    t.start()
+    create_s = []
+    try:
+        for it in range(1000):
+            t0 = time.perf_counter()
+            v.CreateBridgePort("host0-4", vf_mac(4))
+            create_s.append(time.perf_counter() - t0)
+            v.DeleteBridgePort("host0-4")
+            if errors:
+                break
+    finally:
+        stop.set()
+        t.join()
+    assert not errors, errors[0]
+    assert launches[0] > 50 and launches[1] > 0 and launches[2] > 0, launches  # both epochs were seen by the data plane
+    assert dp.stat("full_commits") == full0, "a bridge-port RPC rebuilt the image"
+    assert dp.stat("incremental_commits") >= 2000
+    med = sorted(create_s)[len(create_s) // 2]
+    assert med < 1e-3, f"median CreateBridgePort took {med * 1e3:.2f} ms"
