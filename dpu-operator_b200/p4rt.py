@@ -270,8 +270,20 @@ class Importer:
         self.entries.append(e)
         return e
 
-    def apply(self, dp) -> dict:
-        nexthop_port, routes, bridge_of, l2, wild = {}, [], {}, [], []
+    def apply(self, dp, vsi_mac: dict | None = None) -> dict:
+        """Stage what the entries mean through the C ABI.  Mapping (in_port = the VSI a frame comes from, output =
+        the vport the action names; the compiled pipeline's apply order is not in the repository, so this is the
+        reading the Intel plugin's own rule sets imply):
+          ipv4_table / ipv6_table + nexthop_table      -> LPM prefix -> the next hop's egress port
+          source_port_to_bridge_map + l2_fwd_rx/tx     -> (in_port of the bridge, dst MAC) -> port
+          tx_source_port (vsi -> source port)          -> names the VSI behind a source port (no rule by itself)
+          source_port_to_pr_map (source port -> port)  -> in_port wildcard rule (priority 10 shape)
+          tx_acc_vsi (vsi -> l2_fwd_and_bypass_bridge) -> in_port wildcard rule
+          vsi_to_vsi_loopback (vsi, target_vsi -> port)-> (in_port, dst MAC of target_vsi) rule; `vsi_mac` supplies the
+                                                          MAC of a VSI (the plugin knows it, the rule string does not)
+        Everything else (LAG, mirror, IPsec, tunnel tables) is kept and reported as unmapped."""
+        vsi_mac = vsi_mac or {}
+        nexthop_port, routes, bridge_of, l2, wild, vsi_of_sp, loops = {}, [], {}, [], [], {}, []
         self.unmapped = []
         for e in self.entries:
             short = e.table[len(_C):] if e.table.startswith(_C) else e.table
@@ -289,7 +301,21 @@ class Importer:
             elif short in ("l2_fwd_rx_table", "l2_fwd_tx_table") and e.action.endswith(".l2_fwd"):
                 l2.append((int.from_bytes(e.field("user_meta.pmeta.bridge_id").value, "big"), e.field("dst_mac").value, e.param("port")))
             elif short == "source_port_to_pr_map" and e.action.endswith("fwd_to_vsi"):
-                wild.append((int.from_bytes(e.field("user_meta.cmeta.source_port").value, "big"), e.param("port")))
+                wild.append(("sp", int.from_bytes(e.field("user_meta.cmeta.source_port").value, "big"), e.param("port")))
+            elif short == "tx_source_port" and e.action.endswith("set_source_port"):
+                v = e.field("vmeta.common.vsi")
+                if int.from_bytes(v.mask, "big") == 0x7FF:  # one VSI per entry, as the VSP writes them
+                    vsi_of_sp[e.param("source_port")] = int.from_bytes(v.value, "big")
+                else:
+                    self.unmapped.append(e)
+            elif short == "tx_acc_vsi" and e.action.endswith("l2_fwd_and_bypass_bridge"):
+                wild.append(("vsi", int.from_bytes(e.field("vmeta.common.vsi").value, "big"), e.param("port")))
+            elif short == "vsi_to_vsi_loopback" and e.action.endswith("fwd_to_vsi"):
+                target = int.from_bytes(e.field("target_vsi").value, "big")
+                if target in vsi_mac:
+                    loops.append((int.from_bytes(e.field("vmeta.common.vsi").value, "big"), bytes(vsi_mac[target]), e.param("port")))
+                else:
+                    self.unmapped.append(e)  # nobody told us which MAC this VSI answers to
             else:
                 self.unmapped.append(e)
         done = dict(lpm=0, l2_exact=0, l2_wildcard=0, unresolved_routes=0)
@@ -304,8 +330,13 @@ class Importer:
                 if b == bridge and in_port != port:
                     dp.l2_rule_add(in_port, port, mac)
                     done["l2_exact"] += 1
-        for in_port, port in wild:
+        for in_port, mac, port in loops:
+            dp.l2_rule_add(in_port, port, mac)
+            done["l2_exact"] += 1
+        for kind, key, port in wild:
+            in_port = vsi_of_sp.get(key, key) if kind == "sp" else key  # a source port stands for the VSI that tx_source_port gave it
             dp.l2_rule_add(in_port, port, None)
             done["l2_wildcard"] += 1
         done["unmapped"] = len(self.unmapped)
+        done["unmapped_tables"] = sorted({e.table[len(_C):] if e.table.startswith(_C) else e.table for e in self.unmapped})
         return done

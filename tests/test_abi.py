@@ -133,11 +133,11 @@ def test_a_deleted_port_takes_its_steering_rules_with_it():
     dp.l2_rule_add(a, c)          # does not name b
     dp.commit()
     img = Image(dp.table_export())
-    assert img.l2(b, bytes(6)) is not None and img.l2(a, mac) & 0xFFFF == b
+    assert img.l2(b, bytes(6)) is not None and (img.l2(a, mac) >> 32) & 0xFFFF == b
     dp.port_del("b")
     assert dp.port_add("new") == b  # the id is recycled
     dp.commit()
     img = Image(dp.table_export())
     assert img.l2(b, bytes(6)) is None, "the new port inherited the deleted port's wildcard rule"
-    assert img.l2(a, mac) & 0xFFFF == c and (img.l2(a, mac) >> 28) & 0xF == sfc.consts.STAGE_L2_WILD  # the MAC rule towards b is gone
+    assert (img.l2(a, mac) >> 32) & 0xFFFF == c and (img.l2(a, mac) >> 28) & 0xF == sfc.consts.STAGE_L2_WILD  # the MAC rule towards b is gone
     assert dp.stat("full_commits") == 1  # L2 edits go into the idle copy, no rebuild

@@ -62,10 +62,13 @@ def test_importer_maps_routes_bridges_and_port_maps_onto_the_dataplane():
     for i in range(32):
         dp.port_add(f"p{i}")  # Intel port numbers are used as port ids one to one
     done = imp.apply(dp)
-    # 3 IPv4 routes + 1 IPv6 route; next hop 9 drops -> that /32 stays unresolved
-    assert done == dict(lpm=3, l2_exact=4, l2_wildcard=2, unresolved_routes=1, unmapped=7)
+    # 3 IPv4 routes + 1 IPv6 route; next hop 9 drops -> that /32 stays unresolved.  tx_acc_vsi is one more in_port
+    # wildcard rule, tx_source_port only names the VSI behind source port 21; the two loopback entries stay unmapped
+    # because no MAC was given for their target VSIs
+    assert done == dict(lpm=3, l2_exact=4, l2_wildcard=3, unresolved_routes=1, unmapped=5,
+                        unmapped_tables=["ipsec_spd", "nexthop_table", "tx_lag_table", "vsi_to_vsi_loopback"])
     assert sorted(e.table.split(".")[-1] for e in imp.unmapped) == [
-        "ipsec_spd", "nexthop_table", "tx_acc_vsi", "tx_lag_table", "tx_source_port", "vsi_to_vsi_loopback", "vsi_to_vsi_loopback"]
+        "ipsec_spd", "nexthop_table", "tx_lag_table", "vsi_to_vsi_loopback", "vsi_to_vsi_loopback"]
     dp.commit()
     # the same rules into the oracle, by hand
     orc = Oracle()
@@ -78,20 +81,22 @@ def test_importer_maps_routes_bridges_and_port_maps_onto_the_dataplane():
             if in_port != port:
                 orc.l2_add(in_port, port, mac, consts.PRIO_MAC, rid)
                 rid += 1
-    orc.l2_add(21, 25, None, consts.PRIO_WILDCARD, rid)
-    orc.l2_add(22, 26, None, consts.PRIO_WILDCARD, rid + 1)
+    orc.l2_add(9, 21, None, consts.PRIO_WILDCARD, rid)       # tx_acc_vsi: everything from VSI 9 goes to port 21
+    orc.l2_add(5, 25, None, consts.PRIO_WILDCARD, rid + 1)   # source port 21 is VSI 5 (tx_source_port): VSI 5 -> port 25
+    orc.l2_add(22, 26, None, consts.PRIO_WILDCARD, rid + 2)  # source port 22: no tx_source_port entry names its VSI
     # compare structure of the image-free rule store through the library's own dump: port list + classify on GPU
     # is covered elsewhere; here the oracle answers for the intended semantics
     A, other = bytes([192, 0, 2, 1]), bytes.fromhex("0200deadbeef")
     frames = [
-        (eth(other, SMAC, 0x0800, ipv4(A, bytes([10, 1, 2, 9]), 6, l4ports(1, 2))), 5, 21, consts.STAGE_LPM4),   # /24 -> nh 7 -> port 21
-        (eth(other, SMAC, 0x0800, ipv4(A, bytes([10, 1, 9, 9]), 6, l4ports(1, 2))), 5, 25, consts.STAGE_LPM4),   # /16 -> nh 8 -> port 25
-        (eth(other, SMAC, 0x0800, ipv4(A, bytes([192, 168, 7, 9]), 6, l4ports(1, 2))), 5, 0, consts.STAGE_MISS),  # next hop drops: unresolved
-        (eth(other, SMAC, 0x86DD, ipv6(bytes(16), bytes.fromhex("20010db8000100000000000000000001"), 6, l4ports(1, 2))), 5, 21, consts.STAGE_LPM6),
+        (eth(other, SMAC, 0x0800, ipv4(A, bytes([10, 1, 2, 9]), 6, l4ports(1, 2))), 6, 21, consts.STAGE_LPM4),   # /24 -> nh 7 -> port 21
+        (eth(other, SMAC, 0x0800, ipv4(A, bytes([10, 1, 9, 9]), 6, l4ports(1, 2))), 6, 25, consts.STAGE_LPM4),   # /16 -> nh 8 -> port 25
+        (eth(other, SMAC, 0x0800, ipv4(A, bytes([192, 168, 7, 9]), 6, l4ports(1, 2))), 6, 0, consts.STAGE_MISS),  # next hop drops: unresolved
+        (eth(other, SMAC, 0x86DD, ipv6(bytes(16), bytes.fromhex("20010db8000100000000000000000001"), 6, l4ports(1, 2))), 6, 21, consts.STAGE_LPM6),
         (eth(bytes.fromhex("001122334455"), SMAC, 0x0806, bytes(28)), 0, 25, consts.STAGE_L2_EXACT),   # bridge 77 member 0
         (eth(bytes.fromhex("001122334455"), SMAC, 0x0806, bytes(28)), 21, 25, consts.STAGE_L2_EXACT),  # MAC rule beats the port map
-        (eth(other, SMAC, 0x0806, bytes(28)), 21, 25, consts.STAGE_L2_WILD),                           # source_port_to_pr_map
+        (eth(other, SMAC, 0x0806, bytes(28)), 5, 25, consts.STAGE_L2_WILD),                            # source_port_to_pr_map via tx_source_port
         (eth(other, SMAC, 0x0806, bytes(28)), 22, 26, consts.STAGE_L2_WILD),
+        (eth(other, SMAC, 0x0806, bytes(28)), 9, 21, consts.STAGE_L2_WILD),                            # tx_acc_vsi
         (eth(other, SMAC, 0x0806, bytes(28)), 7, 0, consts.STAGE_MISS),
     ]
     hdr = np.frombuffer(b"".join(f for f, *_ in frames), np.uint8).reshape(-1, 64)
@@ -102,7 +107,7 @@ def test_importer_maps_routes_bridges_and_port_maps_onto_the_dataplane():
     from test_image_walk import Image
 
     img = Image(dp.table_export())
-    assert img.lpm4[4] == 2 and img.lpm6[4] == 1 and img.l2x_cnt == 4 and img.l2w_cnt == 2
+    assert img.lpm4[4] == 2 and img.lpm6[4] == 1 and img.l2x_cnt == 4 and img.l2w_cnt == 3
     assert img.lpm(4, [0x0A010209, 0, 0, 0]) & 0xFFFF_0000_0000 == 21 << 32
     assert img.lpm(4, [0x0A010909, 0, 0, 0]) & 0xFFFF_0000_0000 == 25 << 32
     assert img.lpm(4, [0xC0A80709, 0, 0, 0]) is None
