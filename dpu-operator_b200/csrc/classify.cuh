@@ -481,13 +481,30 @@ __device__ __forceinline__ void fold_counters(unsigned long long* scnt, uint32_t
     }
 }
 
+// COUNTERS: per-rule hit counters (ACL and L2 rules).  A few rules take most of the hits, and same-address
+// atomics from 148 SMs serialise in one L2 slice (27 M of them cost configs[4] 14 ms), so each CTA keeps a small
+// direct-mapped cache of counters in shared memory — key = counter index + 1, claimed with a CAS — and only a
+// rule whose slot is taken by another rule goes to global memory at once.  The cache is added to the global
+// counters when the CTA ends.
+constexpr int kRuleCacheSlots = 64;
+__device__ __forceinline__ void count_rule(unsigned long long* global, uint32_t* ckey, uint32_t* cval, uint32_t idx) {
+    const uint32_t slot = idx & (kRuleCacheSlots - 1), want = idx + 1u;
+    uint32_t k = *(volatile uint32_t*)(ckey + slot);
+    if (k == 0u) {
+        k = atomicCAS(ckey + slot, 0u, want);
+        if (k == 0u) k = want;
+    }
+    if (k == want) atomicAdd(cval + slot, 1u);
+    else atomicAdd(global + idx, 1ull);
+}
+
 // ------------------------------------------------------------------ the kernel -----------
 template <int TILE, int STAGES, bool ACL>
 struct SmemLayout {
     static constexpr int kTileBytes = TILE * 64;
     static constexpr int kAclBytes = ACL ? (TILE / 32) * kAclKeyRows * 32 * 4 : 0;
     static constexpr int kBytes = STAGES * kTileBytes + kAclBytes + 2 * STAGES * 8 + 16 * 8 + 32 * 4 + STAGES * 4 + 16 +
-                                  STAGES * (int)sizeof(StageInfo) + (TILE / 32) * 8 + 1024;
+                                  STAGES * (int)sizeof(StageInfo) + (TILE / 32) * 8 + 2 * kRuleCacheSlots * 4 + 1024;
 };
 
 template <int TILE, int STAGES, bool COUNTERS, bool ACL, bool MULTI = false, int OCC = 0, int FMT = 1>
@@ -517,6 +534,8 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS || FM
     uint32_t* tile_of = dep_sink + 32;                                 // tile index held by each stage
     StageInfo* info = (StageInfo*)(((uintptr_t)(tile_of + STAGES) + 15) & ~(uintptr_t)15);
     uint64_t** wres = (uint64_t**)(info + STAGES);  // MULTI: result base of the tile each consumer warp is working on
+    uint32_t* ckey = (uint32_t*)(wres + TILE / 32);  // COUNTERS: per-rule counter cache (count_rule)
+    uint32_t* cval = ckey + kRuleCacheSlots;
 
     const int tid = threadIdx.x;
     constexpr int kConsumerWarps = TILE / 32;
@@ -530,6 +549,7 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS || FM
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (COUNTERS && tid < 16) scnt[tid] = 0;
+    if (COUNTERS && tid < 2 * kRuleCacheSlots) ckey[tid] = 0;  // keys and values are adjacent
     __syncthreads();
 
     if (tid >= TILE) {
@@ -753,7 +773,7 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS || FM
                 }
                 if (best != 0xFFFFFFFFu) {
                     const uint32_t r = __ldg(T.acl_res + best);
-                    if (COUNTERS) atomicAdd(T.counters + SFC_CNT_RULES0 + (r & 0x0FFFFFFFu), 1ull);
+                    if (COUNTERS) count_rule(T.counters, ckey, cval, SFC_CNT_RULES0 + (r & 0x0FFFFFFFu));
                     if (r & 0x80000000u) {
                         rhi = res_hi(SFC_ACT_DROP, SFC_NF_NONE, 0);
                         rlo = res_lo(SFC_STAGE_ACL, r);
@@ -795,7 +815,7 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS || FM
                         rlo = e.z;
                         rhi = e.w;
                         done = true;
-                        if (COUNTERS) atomicAdd(T.counters + SFC_CNT_L2_0 + ((e.z & 0x0FFFFFFFu) % SFC_CNT_L2_N), 1ull);
+                        if (COUNTERS) count_rule(T.counters, ckey, cval, SFC_CNT_L2_0 + ((e.z & 0x0FFFFFFFu) % SFC_CNT_L2_N));
                         break;
                     }
                     i = (i + 1) & T.l2x_mask;
@@ -807,7 +827,7 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS || FM
                     rhi = e.x;
                     rlo = e.y;
                     done = true;
-                    if (COUNTERS) atomicAdd(T.counters + SFC_CNT_L2_0 + ((e.y & 0x0FFFFFFFu) % SFC_CNT_L2_N), 1ull);
+                    if (COUNTERS) count_rule(T.counters, ckey, cval, SFC_CNT_L2_0 + ((e.y & 0x0FFFFFFFu) % SFC_CNT_L2_N));
                 }
             }
         }
@@ -859,6 +879,7 @@ __global__ void __launch_bounds__(TILE + 32, OCC ? OCC : ((ACL || COUNTERS || FM
         // consumers only (the producer warp has left): named barrier over the TILE consumer threads
         asm volatile("bar.sync 1, %0;" ::"n"(TILE));
         if (tid < 16 && scnt[tid]) atomicAdd(T.counters + tid, scnt[tid]);
+        if (tid < kRuleCacheSlots && ckey[tid] && cval[tid]) atomicAdd(T.counters + (ckey[tid] - 1u), (unsigned long long)cval[tid]);
     }
 }
 

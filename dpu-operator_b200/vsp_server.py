@@ -185,15 +185,39 @@ class B200Vsp:
             ctx.abort(grpc.StatusCode.INTERNAL, "device Store is empty")  # marvell/main.go:625-627
         out = msg("Vendor.DeviceListResponse")()
         if self.dpu_mode:  # the NF-side interfaces (marvell/main.go:628-634)
+            # the reference reports the constant "Healthy" (:219-236 derive it from link state); here the string
+            # says whether the GPU dataplane behind the interfaces still answers (the device plugin withdraws
+            # devices whose health is anything else)
+            health = "Healthy" if self.stats() is not None else "Unhealthy"
             for _, (nf_name, _) in sorted(self.nf_devices.items()):
                 out.devices[nf_name].ID = nf_name
-                out.devices[nf_name].health = "Healthy"
+                out.devices[nf_name].health = health
         else:  # host side: one device per VF (marvell/main.go:635-641); ids are positional here
             for i in range(self.num_vfs):
                 vf = f"host-vf{i}"
                 out.devices[vf].ID = vf
                 out.devices[vf].health = "Healthy"
         return out
+
+    def stats(self):
+        """Dataplane hit counters as a dict — packets per action and per stage since the last reset, read back from
+        the GPU (SFC_CNT_*; counted by launches that pass SFC_F_COUNTERS).  The p4info of the Intel pipeline declares
+        direct counters that p4rt-ctl can read (cmd/intelvsp/p4rt-ctl:1686-1808); the reference daemon never reads
+        them, so there is no RPC for this: it is the stat surface of this VSP for whoever embeds it.  Returns None if
+        the dataplane does not answer; an offline dataplane (no GPU, rule staging only) reports zeros."""
+        from . import consts
+        try:
+            dp = self.vsp.dataplane
+        except SfcError:
+            return None
+        try:
+            c = dp.counters_read(16) if dp.device >= 0 else [0] * 16
+        except SfcError:
+            return None
+        names = ["miss", "acl", "flow", "l2_exact", "l2_wildcard", "lpm4", "lpm6"]
+        return dict(to_cp=int(c[consts.CNT_ACTION0]), forward=int(c[consts.CNT_ACTION0 + 1]), drop=int(c[consts.CNT_ACTION0 + 2]),
+                    by_stage={n: int(c[consts.CNT_STAGE0 + i]) for i, n in enumerate(names)},
+                    table_epoch=dp.table_epoch, table_bytes=dp.table_size)
 
     def SetNumVfs(self, req, ctx):
         if self.dpu_mode:
