@@ -1154,6 +1154,24 @@ const char* validate_image(const uint8_t* img, size_t len) {
         for (uint64_t i = 0; i <= H.l2x_mask; ++i) used += x[i].res_hi != 0;
         if (used > ((uint64_t)H.l2x_mask + 1) / 2) return "image: the L2 exact table has too few empty entries";
     }
+    // result words stored in the tables: the counting code indexes small arrays with their action and stage
+    auto res_ok = [](uint32_t hi, uint32_t lo) { return (hi >> 24) <= SFC_ACT_DROP && (lo >> 28) <= SFC_STAGE_LPM6; };
+    {
+        const L2Entry* x = (const L2Entry*)(img + H.l2x_off);
+        for (uint64_t i = 0; i <= H.l2x_mask; ++i)
+            if (x[i].res_hi && !res_ok(x[i].res_hi, x[i].res_lo)) return "image: an L2 entry holds an unknown action or stage";
+        const L2Wild* w = (const L2Wild*)(img + H.l2w_off);
+        for (uint32_t i = 0; i < H.l2w_n; ++i)
+            if (w[i].res_hi && !res_ok(w[i].res_hi, w[i].res_lo)) return "image: an L2 entry holds an unknown action or stage";
+        if (H.flow_format == kFlowFormatSector) {
+            const uint32_t* f4 = (const uint32_t*)(img + H.flow4_off);
+            for (uint64_t i = 0; i < (uint64_t)H.flow4_nbuckets * H.flow4_slots; ++i)
+                if ((f4[i * 8 + 3] & kSlotValid) && !res_ok(f4[i * 8 + 4], f4[i * 8 + 5])) return "image: a flow slot holds an unknown action or stage";
+            const uint32_t* f6 = (const uint32_t*)(img + H.flow6_off);
+            for (uint64_t i = 0; i < (uint64_t)H.flow6_nbuckets * H.flow6_slots; ++i)
+                if ((f6[i * 16 + 9] & kSlotValid) && !res_ok(f6[i * 16 + 10], f6[i * 16 + 11])) return "image: a flow slot holds an unknown action or stage";
+        }
+    }
     if (H.flow_format != kFlowFormatSector && H.flow_format != kFlowFormatIndexed) return "image: unknown flow table format";
     if (H.flow_format == kFlowFormatIndexed) {
         if (H.fidx_bits < 1 || H.fidx_bits > 27 || !H.fidx_nbuckets || ((uint64_t)H.frec_units + 1) >= (1ull << H.fidx_bits) ||
@@ -1166,6 +1184,15 @@ const char* validate_image(const uint8_t* img, size_t len) {
             for (int sl = 0; sl < kFidxEntries; ++sl) {
                 const uint32_t v = e[b * kFidxBucketWords + sl];
                 if (v && ((v & mask) == 0 || (v & mask) - 1u >= H.frec_units)) return "image: a flow index entry points outside the record array";
+            }
+        const uint32_t* u = (const uint32_t*)(img + H.frec_off);
+        for (uint64_t i = 0; i < H.frec_units; ++i)
+            if ((u[i * 8] & kSlotValid) && !res_ok(u[i * 8 + 2], u[i * 8 + 3])) {
+                // the second unit of an IPv6 record holds address words, not a tag: only units an index entry names count
+                bool named = false;
+                for (uint64_t b = 0; b < (uint64_t)H.fidx_nbuckets * kFidxBucketWords && !named; ++b)
+                    named = (b % kFidxBucketWords) < (uint64_t)kFidxEntries && e[b] && (e[b] & mask) - 1u == i;
+                if (named) return "image: a flow record holds an unknown action or stage";
             }
     }
 

@@ -244,9 +244,24 @@ int sfc_clear(sfc_handle* h);
 
 /* ---------------------------------------------------------------- commit / image -------- */
 
-/* Build the device image from the staged rule set and make it the one sfc_classify uses.
- * Synchronises the device once (the previous image is released).  No reference counterpart:
- * OVS applies each `add-flow` immediately; here edits are batched into epochs. */
+/* Make the staged rule set the one sfc_classify uses.  No reference counterpart: OVS applies each `add-flow`
+ * immediately; here edits are batched into epochs.  What a commit costs depends on what changed since the last one:
+ *   - flows added / deleted, L2 steering rules added / deleted (what the reference really churns: three rules per
+ *     bridge port, marvell/main.go:383-403, 441-460): the sectors of the committed image that changed are patched
+ *     in place (flows) or written into the idle one of two copies of the L2 tables, which then becomes the active
+ *     one.  Tens of microseconds; no rebuild, no allocation once the staging buffers exist.
+ *   - anything else (LPM, ACL, the chain, table-shape options), or a table that has to grow: the image is rebuilt
+ *     on the host and uploaded next to the old one.
+ * Classify calls may run on other threads and streams while a commit is in progress.  A launch sees exactly one
+ * table descriptor: the new image (or L2 copy) is published only after it has landed on the device, and the old
+ * image is released only after every launch that could still read it has finished (the committing thread waits
+ * for the device; data-plane threads are not held up).  Flow patches are the exception: they change the live
+ * table sector by sector, so a launch running beside the commit may see a flow either present or absent per
+ * packet (each packet's answer is that of the rule set before or after the commit, never anything else), and a
+ * flow that the insertion moved between its two buckets can be missed by such a launch; order commits against
+ * launches with sfc_commit_stream or a stream wait if that matters.
+ * If a commit fails (for example no device memory for the second image) the committed image, the staged rules and
+ * the edit log are unchanged, and the next commit tries again. */
 int sfc_commit(sfc_handle* h);
 
 /* Same, ordered on a stream instead of synchronising the device: when only flows were added or
@@ -272,6 +287,11 @@ uint64_t sfc_table_epoch(const sfc_handle* h);
 /* Copy the committed image to / from caller memory.  The *_device variants take device
  * pointers on the handle's device so an NCCL broadcast can move the image rank to rank without
  * a host bounce.  An imported image replaces the committed one (staged rules are untouched).
+ * sfc_table_import checks everything the kernel follows — section bounds and alignment, every index of the
+ * LPM tries, the ACL forest and the flow index, the fill of the L2 table, the action and stage of every stored
+ * result — and refuses a damaged image with -EINVAL.  sfc_table_import_device checks the header only (magic,
+ * version, length): it is meant for images another handle of this library exported (rank-to-rank broadcast);
+ * bring an image of unknown origin in through sfc_table_import.
  * No reference counterpart (single-DPU control plane). */
 int sfc_table_export(const sfc_handle* h, void* buf, size_t len);
 int sfc_table_import(sfc_handle* h, const void* buf, size_t len);
