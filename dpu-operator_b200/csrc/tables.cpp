@@ -746,6 +746,7 @@ struct AclBuilder {
         uint32_t val[kAclKeyWords], mask[kAclKeyWords];
     };
     int bits_per_node = 5;
+    bool one_word = false;
     std::vector<R> rules;           // by rank
     std::vector<AclEntry> nodes;    // child arrays, 2^bits entries each
     std::vector<uint16_t> leaves;   // overflow lists: count, candidates beyond the sixth
@@ -836,6 +837,7 @@ struct AclBuilder {
             int best = -1;
             for (int b = 0; b < kAclKeyBits; ++b) {
                 if (!progress[b] || bit(fixed, b)) continue;
+                if (one_word && nchosen && (b >> 5) != (chosen[0] >> 5)) continue;  // all bits of a node from one key word
                 bool used = false;
                 for (int q = 0; q < nchosen; ++q) used = used || chosen[q] == b;
                 if (!used && (best < 0 || worst[b] < worst[best])) best = b;
@@ -921,6 +923,7 @@ void build_acl(Blob& blob, const std::vector<AclRec>& recs, ImageHeader& H) {
         B.rules = rules;
         B.bits_per_node = force_bits ? std::min(std::max(atoi(force_bits), 1), kAclMaxNodeBits) : (force ? 4 : node_bits[attempt]);
         B.budget_bytes = (force || attempt == 5) ? ~(size_t)0 : budget;
+        B.one_word = getenv("SFC_ACL_ONEWORD") != nullptr;
         std::vector<std::vector<uint16_t>> cat(8);
         for (uint32_t i = 0; i < n; ++i) {
             const uint32_t* m = rules[i].mask;
