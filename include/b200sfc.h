@@ -407,8 +407,11 @@ const char* sfc_group_last_error(const sfc_group* g);
  * together with the packet buffers, and the library keeps what it needs on the GPU in a fixed
  * array that is part of the library image itself:
  *
- *   SFC_STATIC_AREA_BYTES of device memory per GPU, present on every GPU that loads the library
- *   from load until the process exits.  The first 256 bytes are the classify kernel's tile-ticket
+ *   SFC_STATIC_AREA_BYTES of device memory per GPU, held on every GPU that loads the library until
+ *   the process exits.  The CUDA runtime sets the array up when the library's code is first loaded
+ *   onto a device — with lazy module loading that is the first call here, or any earlier kernel
+ *   launch of this library, on that device — so that one call can fail for lack of memory; no later
+ *   call can.  The first 256 bytes are the classify kernel's tile-ticket
  *   scratch; the rest holds the table image, so an image may be at most
  *   SFC_STATIC_AREA_BYTES - 256 bytes (a steering set plus tens of thousands of flows).  A larger
  *   image is refused with -E2BIG and a message naming both sizes; nothing is truncated.
@@ -417,6 +420,8 @@ const char* sfc_group_last_error(const sfc_group* g);
  *   - hdr / in_port / result are DEVICE pointers as for sfc_classify; image_host is a HOST pointer.
  *     Pass image_host == NULL to classify against the image the previous call left on that device.
  *   - asynchronous on cuda_stream; results are bit-identical to sfc_classify with the same image.
+ *     (An image_host in pageable memory makes the copy wait for earlier work on the stream and return
+ *     only when the bytes have left the buffer; pass pinned memory, or NULL, to stay asynchronous.)
  *   - the FIRST call on each device also does one-time set-up (looks up the array's device
  *     address, raises the kernel's shared-memory limit).  Make that first call before starting any
  *     stream capture on the device; later calls only copy, clear and launch.
@@ -437,7 +442,8 @@ int sfc_classify_static(int device, const void* image_host, size_t image_bytes, 
 /* ---------------------------------------------------------------- synthetic traffic ----- */
 
 /* Fill device buffers with the deterministic synthetic workload of SURVEY.md §8(d) (counter-based
- * splitmix64; the same arithmetic is restated in oracle/sfc_oracle.cpp and in numpy for tests).
+ * splitmix64; the same workload is written a second time, independently, in oracle/workload.cpp, and
+ * tests/test_oracle.py holds the two to identical bytes).
  * `spec` is an sfc_gen_spec; packets [first, first+n) of the stream are produced. */
 typedef struct sfc_gen_spec {
     uint64_t seed_pkts;      /* packet stream seed                          */
