@@ -350,6 +350,11 @@ class Ctx:
         oh, op = self.orc.OracleGen.packets(spec, first_packet, n)
         want, cnt = stager.orc.classify(oh, op, threads=self.cpu_threads, counters=True)
         bad = int((got != want).sum())
+        if self.world > 1 and not getattr(self, "_reduce_warm", False):
+            # the first all-reduce of a process sets NCCL's channels up: do it on a scratch tensor, so that the one
+            # timed below is the steady-state cost of summing the counters
+            self.sum_over_ranks(np.zeros(self.sfc.consts.CNT_TOTAL, dtype=np.uint64))
+            self._reduce_warm = True
         reduce_ms = self.group.reduce_counters(dp, self.world) if self.world > 1 else 0.0
         have = dp.counters_read()
         total = self.sum_over_ranks(cnt)

@@ -334,10 +334,15 @@ __device__ __forceinline__ bool flow4_lookup(const DevTables& T, const Key& k, u
     rlo = s[5];
     return hit;
 }
-__device__ __forceinline__ bool flow6_probe(const uint32_t* p, const Key& k, uint32_t tag, uint32_t& rhi, uint32_t& rlo) {
+__device__ __forceinline__ bool flow6_probe(const uint32_t* p, const Key& k, uint32_t tag, uint32_t& rhi, uint32_t& rlo, bool l1) {
     uint32_t s[16];
-    ldg256(p, s);
-    ldg256(p + 8, s + 8);
+    if (l1) {
+        ldg256_l1(p, s);
+        ldg256_l1(p + 8, s + 8);
+    } else {
+        ldg256(p, s);
+        ldg256(p + 8, s + 8);
+    }
     bool eq = s[8] == k.ports && s[9] == tag;
 #pragma unroll
     for (int i = 0; i < 4; ++i) eq = eq && s[i] == k.sip[i] && s[4 + i] == k.dip[i];
@@ -352,8 +357,9 @@ __device__ __forceinline__ bool flow6_lookup(const DevTables& T, const Key& k, u
     bool hit = false;
     for (uint32_t j = 0; j < T.flow6_nhash && !hit; ++j) {
         const uint32_t* p = T.flow6 + (size_t)flow_bucket(x, y, (int)j, T.S6 + 10, T.flow6_nbuckets) * (kFlow6BucketWords * T.flow6_slots);
-        hit = flow6_probe(p, k, tag, rhi, rlo);
-        if (!hit && T.flow6_slots == 2) hit = flow6_probe(p + kFlow6BucketWords, k, tag, rhi, rlo);
+        const bool l1 = (T.flow4_mode & kProbeL1) != 0;
+        hit = flow6_probe(p, k, tag, rhi, rlo, l1);
+        if (!hit && T.flow6_slots == 2) hit = flow6_probe(p + kFlow6BucketWords, k, tag, rhi, rlo, l1);
     }
     return hit;
 }

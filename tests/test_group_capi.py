@@ -102,4 +102,5 @@ def test_c_host_program_drives_the_gpus(torch_cuda, tmp_path):
     n = min(torch_cuda.cuda.device_count(), 2)
     out = subprocess.run([str(exe), str(n)], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr
-    assert out.stdout.startswith(f"group_demo ok: {n} GPUs")
+    # NCCL prints its version banner to stdout on some hosts before the program's own line
+    assert any(line.startswith(f"group_demo ok: {n} GPUs") for line in out.stdout.splitlines()), out.stdout
