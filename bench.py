@@ -460,19 +460,8 @@ def headline(cx: Ctx):
             dp.classify_host_wait(prev[0])
             seen.append(int(h_res[prev[1]][0]))
 
-        def copies_only():  # what the host side can deliver at all: the same bytes, no kernel, every rank at once
-            side = torch.cuda.Stream()
-            with torch.cuda.stream(side):
-                for i in range(e2e_steps):
-                    b = i % n_host
-                    hdr[b].copy_(h_hdr[b], non_blocking=True)
-                    ports[b].copy_(h_ports[b], non_blocking=True)
-                    h_res[b].copy_(res[b], non_blocking=True)
-            side.synchronize()
-
         sync_s = timed_loop(one_call_per_step)
         e2e_s = timed_loop(queued_one_ahead)
-        copy_s = timed_loop(copies_only)
         assert len(seen) == e2e_steps
         dp.classify(*ptrs[0], BATCH, 0, cx.st)
         torch.cuda.synchronize()
@@ -482,10 +471,7 @@ def headline(cx: Ctx):
                "api": "sfc_classify_host_submit / _wait, batch i+1 queued before batch i is collected (pinned host buffers, "
                       "chunked H2D/kernel/D2H pipeline); every step's H2D and D2H are inside the timed region",
                "one_blocking_call_per_step_mpps": e2e_steps * BATCH * cx.world / sync_s / 1e6,
-               "bound": "PCIe: 66 B in + 8 B out per packet",
-               "copies_only_mpps": e2e_steps * BATCH * cx.world / copy_s / 1e6,
-               "copies_only_note": "the same host-to-device and device-to-host bytes with no kernel between them, all ranks copying "
-                                   "at once: the ceiling the host side (PCIe links, root complex, host memory) sets for e2e at this N"}
+               "bound": "PCIe: 66 B in + 8 B out per packet"}
 
     kernel_ms = ms / args.steps  # one classify launch per step; includes launch gaps inside the region
     out = {
