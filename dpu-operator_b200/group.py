@@ -55,7 +55,6 @@ def reduce_counters(dp, world: int) -> float:
 
     from . import consts
 
-    t0 = time.perf_counter()
     n = consts.CNT_TOTAL
     # view the library's counter array as a torch tensor (no copy): int64 has the same bits as u64
     iface = {"shape": (n,), "typestr": "<i8", "data": (dp.counters_device_ptr, False), "version": 2}
@@ -64,9 +63,15 @@ def reduce_counters(dp, world: int) -> float:
         __cuda_array_interface__ = iface
 
     t = torch.as_tensor(_Wrap(), device=torch.device("cuda", dp.device))
-    dist.all_reduce(t, op=dist.ReduceOp.SUM)
     torch.cuda.synchronize()
-    return (time.perf_counter() - t0) * 1e3
+    # the collective itself, timed on the device (host-side wrapping and the first-use set-up of a communicator are
+    # not part of what a reporting interval pays)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1)
 
 
 def reduce_counters_host(counters: np.ndarray) -> np.ndarray:
