@@ -130,3 +130,23 @@ def test_the_two_writings_of_the_workload_agree_byte_for_byte():
         if na:
             assert OracleGen.acl_rules(spec, na).tobytes() == sfc.gen_acl_rules(spec, na).tobytes()
     assert all(OracleGen.mac(i) == sfc.gen_mac(i) for i in (0, 1, 7, 255, 256, 70000))
+
+
+def test_reference_arm_of_the_bench_loads_no_product_code():
+    """`bench.py --impl reference` times the CPU oracle on inputs from the oracle's own generator.  With the product
+    library made unloadable the arm must still run (importing the package would raise), and its line must carry the
+    keys the driver reads."""
+    import subprocess
+    import sys
+
+    env = dict(os.environ, B200SFC_LIB="/nonexistent/libb200sfc.so")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                         capture_output=True, text=True, timeout=300, env=env)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "Mpps" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
+    assert line["config"]["workload"].startswith("configs[1]")
+    # and the GPU arm names the same workload (the driver compares the two strings)
+    src = open(os.path.join(ROOT, "bench.py")).read()
+    assert src.count('"workload": WORKLOAD') == 2
