@@ -741,7 +741,8 @@ void acl_key_words(const sfc_acl_rule& r, uint32_t* val, uint32_t* mask) {
 }
 
 struct AclBuilder {
-    static constexpr int kLeafMax = 8, kMaxDepth = 12;
+    static constexpr int kMaxDepth = 12;
+    int kLeafMax = 8;  // a sub-problem this small becomes a leaf
     struct R {
         uint32_t val[kAclKeyWords], mask[kAclKeyWords];
     };
@@ -924,6 +925,7 @@ void build_acl(Blob& blob, const std::vector<AclRec>& recs, ImageHeader& H) {
         B.bits_per_node = force_bits ? std::min(std::max(atoi(force_bits), 1), kAclMaxNodeBits) : (force ? 4 : node_bits[attempt]);
         B.budget_bytes = (force || attempt == 5) ? ~(size_t)0 : budget;
         B.one_word = getenv("SFC_ACL_ONEWORD") != nullptr;
+        if (const char* lf = getenv("SFC_ACL_LEAF")) B.kLeafMax = std::min(std::max(atoi(lf), 1), 64);
         std::vector<std::vector<uint16_t>> cat(8);
         for (uint32_t i = 0; i < n; ++i) {
             const uint32_t* m = rules[i].mask;
