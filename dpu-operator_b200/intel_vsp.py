@@ -7,6 +7,10 @@ Reference: vendored github.com/intel/ipu-opi-plugins/ipu-plugin, pkg/p4rtclient/
   programVsiToVsiP4Rules     :412-444   two loopback entries per VSI pair
   AddNFP4Rules               :819-859   2 x programNfPrVportP4Rules, then every VF x {ingress, egress}
   AddPeerToPeerP4Rules       :903-919   every unordered pair of host VFs
+  programPhyVportP4Rules     :123-181   a physical port and the port representor that fronts it
+  AddLAGP4Rules              :939-976   the LPM root look-up entry and the eight LAG hash buckets
+  AddRHPrimaryNetworkVportP4Rules :1017-1089  mirror profile, primary-network bridge and MAC entry
+(the last three look a VSI up on the IMC over ssh, `ImcQueryfindVsiGivenMacAddr`; here the VSI is an argument)
 and pkg/utils/utils.go :39 (vsiToVportOffset), :76-85 (ExtractVsiVportInfo: VSI = second MAC octet), :105-107.
 
 The reference is Go and executes `p4rt-ctl add-entry br0 <table> "<rule>"` once per entry; here the builders
@@ -19,6 +23,7 @@ fmt.Sprintf calls out of the Go source.
 from __future__ import annotations
 
 VSI_TO_VPORT_OFFSET = 16  # utils.go:39
+MIRROR_PROFILE_ID, BRIDGE_ID, PHY_PORT = 3, 0, 0  # p4rtclient.go:30-33
 _C = "linux_networking_control."
 
 
@@ -91,6 +96,39 @@ def add_peer_to_peer_p4_rules(vf_macs) -> list[tuple[str, str]]:
         for j in range(i + 1, len(vf_macs)):
             out += program_vsi_to_vsi_p4_rules(vf_macs[i], vf_macs[j])
     return out
+
+
+def program_phy_vport_p4_rules(phy_port: int, pr_vsi: int) -> list[tuple[str, str]]:
+    """programPhyVportP4Rules (:123-181); pr_vsi is what the IMC reports for the port representor's MAC."""
+    pr_vport = pr_vsi + VSI_TO_VPORT_OFFSET
+    return [
+        (_C + "rx_source_port", f"vmeta.common.port_id={phy_port},zero_padding=0,action={_C}set_source_port({phy_port})"),
+        (_C + "source_port_to_pr_map", f"user_meta.cmeta.source_port={phy_port},zero_padding=0,action={_C}fwd_to_vsi({pr_vport})"),
+        (_C + "tx_acc_vsi", f"vmeta.common.vsi={pr_vsi},zero_padding=0,action={_C}l2_fwd_and_bypass_bridge({phy_port})"),
+    ]
+
+
+def add_lag_p4_rules() -> list[tuple[str, str]]:
+    """AddLAGP4Rules (:939-976): 1 + 8 entries."""
+    out = [(_C + "ipv4_lpm_root_lut", f"user_meta.cmeta.bit16_zeros=4/65535,priority=2048,action={_C}ipv4_lpm_root_lut_action(0)")]
+    for idx in range(8):
+        out.append((_C + "tx_lag_table", f"user_meta.cmeta.lag_group_id=0/255,hash={idx}/7,priority=1,action={_C}bypass"))
+    return out
+
+
+def add_rh_primary_network_vport_p4_rules(d4_vsi: int, d1_vsi: int, d1_mac) -> list[tuple[str, str]]:
+    """AddRHPrimaryNetworkVportP4Rules (:1017-1089); the two VSIs are what the IMC reports for the D4 and D1 MACs,
+    the MAC goes into the rule with its colons stripped (getStrippedMacAndVsi :103-121)."""
+    mac = mac_bytes(d1_mac).hex()
+    return [
+        (_C + "mir_prof", f"mirror_prof_key={MIRROR_PROFILE_ID},action={_C}mir_prof_action(vport_id={d1_vsi},mode=0,port_dest_type=0,"
+                          f"dest_id={d1_vsi},func_valid=1,store_vsi=1)"),
+        (_C + "rx_phy_port_to_pr_map", f"vmeta.common.port_id=0x00,zero_padding=0x0000,action={_C}mirror_and_send({d4_vsi + 16},{MIRROR_PROFILE_ID})"),
+        (_C + "tx_acc_vsi", f"vmeta.common.vsi={d1_vsi},zero_padding=0,action={_C}l2_fwd_and_bypass_bridge({PHY_PORT})"),
+        (_C + "source_port_to_bridge_map", f"user_meta.cmeta.source_port={PHY_PORT}/0xffff,hdrs.vlan_ext[vmeta.common.depth].hdr.vid={PHY_PORT}/0xfff,"
+                                           f"priority=1,action={_C}set_bridge_id(bridge_id={BRIDGE_ID})"),
+        (_C + "l2_fwd_rx_table", f"user_meta.pmeta.bridge_id={BRIDGE_ID},dst_mac=0x{mac},action={_C}l2_fwd({d1_vsi + 16})"),
+    ]
 
 
 class IntelVsp:

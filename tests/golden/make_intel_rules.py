@@ -88,12 +88,45 @@ for vf, acc in zip(vf_macs, acc_macs):  # CreateBridgePort x 8 (bridgeport.go:15
     stream += host_vf(vf, acc)
 stream += add_nf(vf_macs, nf_macs["ingress"], nf_macs["egress"], nf_macs["ingress_pr"], nf_macs["egress_pr"])  # CreateNetworkFunction
 p2p = peer_to_peer(vf_macs)
+# ---- the three builders that take their VSIs from the IMC: evaluated with the VSIs given, constants read from the file ----
+CONSTS = {k: int(v) for k, v in re.findall(r"^\t(mirror_profile_id|bridgeId|phyPort)\s*=\s*(\d+)", SRC, re.M)}
+assert set(CONSTS) == {"mirror_profile_id", "bridgeId", "phyPort"}
+
+
+def run_imc(func, env):
+    """Evaluate the add-entry Sprintf calls of `func` with the Go expressions in `env` (name -> value); literals pass through."""
+    _, text = body(func)
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)  # rule sets kept "for reference only" inside comments
+    out = []
+    for control, meta in re.findall(r'Action:\s+"add-entry",\s+P4br:\s+"br0",\s+Control:\s+"([\w.]+)",\s+Metadata:\s+(.*?),\n\t+\}', text, re.S):
+        m = re.match(r'fmt\.Sprintf\(\s*"([^"]+)",\s*(.*?),?\s*\)$', meta.strip(), re.S)
+        if not m:
+            out.append([control, meta.strip().strip('"')])
+            continue
+        fmt, args = m.group(1), [a.strip() for a in m.group(2).split(",") if a.strip()]
+        vals = [eval(a, {}, dict(CONSTS, **env)) for a in args]  # the arguments are names or `name+16`
+        out.append([control, fmt % tuple(vals)])
+    return out
+
+
+phy = run_imc("programPhyVportP4Rules", dict(phyPort=0, prVsi=0x0a, prVport=0x0a + OFFSET))
+# AddLAGP4Rules: one literal entry, then `for idx := 0; idx < 8; idx++` around one Sprintf — the loop is unrolled here
+assert re.search(r"for idx := 0; idx < 8; idx\+\+", body("AddLAGP4Rules")[1])
+lag = []
+for idx in range(8):
+    both = run_imc("AddLAGP4Rules", dict(idx=idx))
+    assert len(both) == 2
+    lag = [both[0]] + lag[1:] + [both[1]]
+rh = run_imc("AddRHPrimaryNetworkVportP4Rules", dict(d4Vsi=0x0c, d1Vsi=0x0d, d1MacAddr="000d00000314"))
+assert len(phy) == 3 and len(lag) == 9 and len(rh) == 5, (len(phy), len(lag), len(rh))
+
 fixture = dict(
     source="vendor/github.com/intel/ipu-opi-plugins/ipu-plugin/pkg/p4rtclient/p4rtclient.go: fmt.Sprintf calls of AddHostVfP4Rules, "
            "programNfPrVportP4Rules, programVsiToVsiP4Rules evaluated; call order of AddNFP4Rules / AddPeerToPeerP4Rules",
     vsi_to_vport_offset=OFFSET, vf_macs=vf_macs, acc_macs=acc_macs, nf_macs=nf_macs,
     formats={f: [[c, fmt, args] for c, fmt, args in builder(f)[1]] for f in ("AddHostVfP4Rules", "programNfPrVportP4Rules", "programVsiToVsiP4Rules")},
     rules_8_host_vfs_then_1_nf=stream, rules_peer_to_peer=p2p,
+    consts=CONSTS, rules_phy_port_0_pr_vsi_10=phy, rules_lag=lag, rules_rh_primary_d4_vsi_12_d1_vsi_13=rh, rh_d1_mac="00:0d:00:00:03:14",
 )
 assert len(stream) == 8 * 5 + 2 * 6 + 8 * 2 * 2 == 84 and len(p2p) == 8 * 7
 path = os.path.join(os.path.dirname(__file__), "intel_rules.json")

@@ -120,3 +120,27 @@ def test_imported_intel_rules_on_the_gpu(torch_cuda):
     stage = sfc.result_fields(got)[3]
     for s in (consts.STAGE_L2_EXACT, consts.STAGE_L2_WILD, consts.STAGE_MISS):
         assert (stage == s).sum() > 1000, f"stage {s} hardly hit"
+
+
+def test_physical_port_lag_and_primary_network_builders_equal_the_go_source():
+    """The three builders that take their VSI from the IMC (programPhyVportP4Rules, AddLAGP4Rules,
+    AddRHPrimaryNetworkVportP4Rules): string for string what the fixture generator evaluated out of the Go source, and
+    every string is accepted by the p4rt-ctl grammar against the reference's p4info."""
+    assert G["consts"] == dict(mirror_profile_id=intel.MIRROR_PROFILE_ID, bridgeId=intel.BRIDGE_ID, phyPort=intel.PHY_PORT)
+    sets = {
+        "rules_phy_port_0_pr_vsi_10": intel.program_phy_vport_p4_rules(0, 10),
+        "rules_lag": intel.add_lag_p4_rules(),
+        "rules_rh_primary_d4_vsi_12_d1_vsi_13": intel.add_rh_primary_network_vport_p4_rules(12, 13, G["rh_d1_mac"]),
+    }
+    for key, mine in sets.items():
+        assert [list(r) for r in mine] == G[key], key
+        for table, rule in mine:
+            e = p4rt.parse_entry(table, rule)
+            assert e.table == table and e.action.startswith("linux_networking_control.")
+    # the primary-network set maps onto the B200 tables too: its bridge member and MAC entry become an exact L2 rule
+    imp = p4rt.Importer()
+    for table, rule in sets["rules_rh_primary_d4_vsi_12_d1_vsi_13"] + sets["rules_phy_port_0_pr_vsi_10"]:
+        imp.add(table, rule)
+    done = imp.apply(sfc.Dataplane(-1))
+    assert done["l2_wildcard"] == 3  # tx_acc_vsi x 2 and source_port_to_pr_map
+    assert done["unmapped_tables"] == ["mir_prof", "rx_phy_port_to_pr_map", "rx_source_port"]
