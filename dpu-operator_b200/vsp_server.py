@@ -272,6 +272,33 @@ def serve(address: str = f"unix:{VENDOR_PLUGIN_SOCKET}", device: int = 0, rpm_po
     return server, vsp
 
 
+class NfMacPairer:
+    """The caller side of CreateNetworkFunction: how the DPU-side daemon turns CNI ADD / DEL of a network function's
+    two interfaces into one RPC each (internal/daemon/dpusidemanager.go:104-139).  MACs are collected per network
+    namespace in arrival order; the second ADD calls CreateNetworkFunction(macs[0], macs[1]) — the daemon ignores that
+    call's error (:115) — and a DEL that finds two MACs calls DeleteNetworkFunction before dropping the newest one.
+    `vsp` is anything with the two methods (a VspClient, a B200Vsp wrapper, a test double)."""
+
+    def __init__(self, vsp):
+        self.vsp = vsp
+        self.mac_store: dict[str, list[str]] = {}
+
+    def cni_add(self, netns: str, mac: str):
+        macs = self.mac_store.setdefault(netns, [])
+        macs.append(mac)
+        if len(macs) == 2:
+            try:
+                self.vsp.CreateNetworkFunction(macs[0], macs[1])
+            except Exception:  # noqa: BLE001  (dpusidemanager.go:115 drops the error)
+                pass
+
+    def cni_del(self, netns: str):
+        macs = self.mac_store.get(netns, [])
+        if len(macs) == 2:
+            self.vsp.DeleteNetworkFunction(macs[0], macs[1])
+        self.mac_store[netns] = macs[:-1]
+
+
 class VspClient:
     """What ``GrpcPlugin`` (internal/daemon/plugin/vendorplugin.go:183-265) does, for tests and demos."""
 

@@ -140,3 +140,32 @@ def test_stat_surface_and_health(vsp):
     assert st["forward"] == 0 and set(st["by_stage"]) == {"miss", "acl", "flow", "l2_exact", "l2_wildcard", "lpm4", "lpm6"}
     devs = client.GetDevices(vs.msg("Vendor.Empty")())
     assert {d.health for d in devs.devices.values()} == {"Healthy"}
+
+
+def test_daemon_side_mac_pairing_drives_the_nf_rpcs(vsp):
+    """dpusidemanager.go:104-139: two CNI ADDs in one netns make ONE CreateNetworkFunction(first MAC, second MAC); the
+    first DEL makes one DeleteNetworkFunction with the same pair, the second DEL none."""
+    client, impl = vsp
+    client.Init(vs.msg("Vendor.InitRequest")(dpu_mode=True))
+    calls = []
+
+    class Spy:
+        def CreateNetworkFunction(self, a, b):
+            calls.append(("create", a, b))
+            client.CreateNetworkFunction(vs.msg("Vendor.NFRequest")(input=a, output=b))
+
+        def DeleteNetworkFunction(self, a, b):
+            calls.append(("delete", a, b))
+            client.DeleteNetworkFunction(vs.msg("Vendor.NFRequest")(input=a, output=b))
+
+    pair = vs.NfMacPairer(Spy())
+    m0, m1 = G["nf_macs"]
+    pair.cni_add("/var/run/netns/nf", m0)
+    assert calls == []
+    pair.cni_add("/var/run/netns/other", "02:00:00:00:09:09")  # another pod's first interface does not complete the pair
+    pair.cni_add("/var/run/netns/nf", m1)
+    assert calls == [("create", m0, m1)]
+    assert any(",actions=output:" + G["rpm_port"] in r for r in impl.vsp.flow_dump())  # the NF's wire rules are programmed
+    pair.cni_del("/var/run/netns/nf")
+    pair.cni_del("/var/run/netns/nf")
+    assert calls == [("create", m0, m1), ("delete", m0, m1)] and pair.mac_store["/var/run/netns/nf"] == []
