@@ -428,7 +428,7 @@ __global__ void gen_kernel(sfc_gen_spec spec, uint64_t first, uint64_t n, uint8_
 // =================================================================== life cycle ==========
 extern "C" {
 
-const char* sfc_version(void) { return "b200sfc 0.8 (image v11)"; }
+const char* sfc_version(void) { return "b200sfc 0.9 (image v12)"; }
 
 int sfc_create(int device_ordinal, sfc_handle** out) {
     if (!out) return -EINVAL;
@@ -1035,7 +1035,7 @@ long sfc_stat(const sfc_handle* h, const char* name) {
     if (!h || !name) return -EINVAL;
     if (!strcmp(name, "full_commits")) return (long)h->n_full_commits;
     if (!strcmp(name, "incremental_commits")) return (long)h->n_incremental_commits;
-    if (!strcmp(name, "patched_buckets")) return (long)h->n_patched_buckets;
+    if (!strcmp(name, "patched_buckets") || !strcmp(name, "patched_sectors")) return (long)h->n_patched_buckets;
     if (!strcmp(name, "flows")) return (long)h->rs.flows.size();
     if (!strcmp(name, "flow4_first_bucket")) return (long)h->flow_first[0];
     if (!strcmp(name, "launches")) return (long)h->launches.load();

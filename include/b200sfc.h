@@ -276,7 +276,8 @@ int sfc_commit(sfc_handle* h);
 int sfc_commit_stream(sfc_handle* h, void* cuda_stream);
 
 /* Counters of the library itself (not of traffic): "full_commits", "incremental_commits",
- * "patched_buckets", "flows", "flow4_first_bucket", "launches".  Negative errno for unknown names.
+ * "patched_sectors" (32-byte sectors shipped by incremental commits; "patched_buckets" is the same number under its
+ * older name), "flows", "flow4_first_bucket", "launches".  Negative errno for unknown names.
  * Reference anchor: the health/stat surface of DeviceService.GetDevices (marvell/main.go:219-236). */
 long sfc_stat(const sfc_handle* h, const char* name);
 
