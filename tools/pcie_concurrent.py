@@ -11,17 +11,19 @@ streams = [torch.cuda.Stream(device=i) for i in range(n)]
 print(json.dumps(dict(gpus_visible=n, cpu_affinity=len(__import__("os").sched_getaffinity(0)))), flush=True)
 k = 1
 while k <= n:
-    for direction in ("h2d", "d2h", "both"):
+    for direction in ("h2d", "d2h"):
         for i in range(k):
             torch.cuda.synchronize(i)
         t0 = time.perf_counter()
         for _ in range(REPS):
             for i in range(k):
                 with torch.cuda.stream(streams[i]):
-                    if direction in ("h2d", "both"):
+                    if direction == "h2d":
                         dev[i].copy_(host[i], non_blocking=True)
-                    if direction == "d2h":
+                    elif direction == "d2h":
                         host[i].copy_(dev[i], non_blocking=True)
+                    else:  # both directions queued on the one stream (they serialise per GPU, as in a simple host loop)
+                        dev[i].copy_(host[i], non_blocking=True)
         for i in range(k):
             streams[i].synchronize()
         dt = time.perf_counter() - t0
