@@ -242,3 +242,77 @@ def test_bridge_port_churn_while_another_thread_classifies(torch_cuda):
     assert dp.stat("incremental_commits") >= 2000
     med = sorted(create_s)[len(create_s) // 2]
     assert med < 1e-3, f"median CreateBridgePort took {med * 1e3:.2f} ms"
+
+
+def test_indexed_table_reuses_record_units_under_mixed_family_churn():
+    """Format 2 with both families: repeated delete / add rounds patch the image in place, every live flow stays
+    findable, every deleted one is gone, and released record units (one per IPv4 flow, a pair per IPv6 flow) are
+    handed out again instead of growing the array."""
+    dp = sfc.Dataplane(-1)
+    dp.set_option("flow_format", 2)
+    spec = config3_spec(n_flows=40000, v6_permille=350, n_ports=8)
+    keys, acts = sfc.gen_flows(spec, 0, 40000)
+    dp.flow_add_bulk(keys[:20000], acts[:20000])
+    dp.commit()
+    used0 = Image(dp.table_export()).frec_used
+    rng = np.random.default_rng(11)
+    alive = set(range(20000))
+    nxt = 20000
+    for rnd in range(5):
+        gone = rng.choice(sorted(alive), 2000, replace=False)
+        for i in gone:
+            dp.flow_del(keys[i])
+            alive.discard(int(i))
+        dp.flow_add_bulk(keys[nxt:nxt + 2000], acts[nxt:nxt + 2000])
+        alive.update(range(nxt, nxt + 2000))
+        nxt += 2000
+        dp.commit()
+        img = Image(dp.table_export())
+        assert img.f4_cnt + img.f6_cnt == len(alive) == 20000
+        for i in list(gone[:300]):
+            assert img.flow(keys[i])[0] is None, (rnd, i)
+        for i in rng.choice(sorted(alive), 600, replace=False):
+            r = img.flow(keys[i])[0]
+            assert r is not None and r & 0x0FFFFFFF != 0xFFFFFFF, (rnd, i)
+    assert (dp.stat("full_commits"), dp.stat("incremental_commits")) == (1, 5)
+    # 10 000 flows were replaced; without reuse the array would have grown by ~13 500 units
+    assert img.frec_used <= used0 + 3000, (used0, img.frec_used)
+
+
+def test_import_refuses_damaged_flow_index_l2_table_and_results():
+    import errno
+    import struct as st
+    sc = Scenario(sfc.Dataplane(-1))
+    sc.dp.set_option("flow_format", 2)
+    topo = sc.build_chain(4, 1)
+    spec = config3_spec(n_flows=3000, v6_permille=300, n_ports=topo["n_ports"])
+    install_flows(sc, spec)
+    sc.dp.commit()
+    good = sc.dp.table_export()
+    img = Image(good)
+    sfc.Dataplane(-1).table_import(good)
+
+    def refused(mutate):
+        bad = good.copy()
+        mutate(bad)
+        with pytest.raises(sfc.SfcError) as e:
+            sfc.Dataplane(-1).table_import(bad)
+        assert e.value.code == -errno.EINVAL
+        return str(e.value)
+
+    def put32(buf, off, v):
+        buf[off:off + 4] = np.frombuffer(st.pack("<I", v), dtype=np.uint8)
+
+    # an index entry naming a unit beyond the record array
+    first = next(o for o in range(img.fidx_off, img.fidx_off + img.fidx_nb * 32, 4) if (o - img.fidx_off) % 32 < 28 and int(img.u32(o, 1)[0]))
+    assert "flow index" in refused(lambda b: put32(b, first, (1 << img.fidx_bits) - 1))
+    # an L2 exact table with no empty entry left (a miss would probe forever)
+    def fill_l2(b):
+        for i in range(img.l2x_mask + 1):
+            put32(b, img.l2x_off + 16 * i + 12, 0x01FF0001)
+    assert "L2" in refused(fill_l2)
+    # a stored result with an action the counters cannot index
+    hit = next(i for i in range(img.l2x_mask + 1) if int(img.u32(img.l2x_off + 16 * i + 12, 1)[0]))
+    assert "unknown action" in refused(lambda b: put32(b, img.l2x_off + 16 * hit + 12, 0x7F000001))
+    # a section offset that is no longer aligned for the kernel's 32-byte loads (header field frec_off at byte 424)
+    assert "aligned" in refused(lambda b: b.__setitem__(slice(424, 432), np.frombuffer(st.pack("<Q", img.frec_off + 8), dtype=np.uint8)))
