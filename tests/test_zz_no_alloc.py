@@ -21,8 +21,9 @@ from common import Scenario, config3_spec, install_flows, install_lpm_acl, sfc
 pytestmark = pytest.mark.gpu
 
 
-def _scenario(n_acl):
+def _scenario(n_acl, fmt=1):
     dp = sfc.Dataplane(0)
+    dp.set_option("flow_format", fmt)
     sc = Scenario(dp)
     topo = sc.build_chain(8, 2)
     spec = config3_spec(n_flows=20000, n_ports=topo["n_ports"] + 2, n_pfx4=500, n_pfx6=100, lpm_permille=600, n_acl=n_acl)
@@ -40,10 +41,10 @@ def _batch(torch, dp, spec, first, n):
     return hdr, ports
 
 
-@pytest.mark.parametrize("n_acl", [0, 120])
-def test_static_entry_point_matches_the_handle_entry_point_twice(torch_cuda, n_acl):
+@pytest.mark.parametrize("n_acl,fmt", [(0, 1), (120, 1), (0, 2)])
+def test_static_entry_point_matches_the_handle_entry_point_twice(torch_cuda, n_acl, fmt):
     torch = torch_cuda
-    dp, sc, spec = _scenario(n_acl)
+    dp, sc, spec = _scenario(n_acl, fmt)  # with / without ACL rules, sector / indexed flow table: four different kernels
     image = dp.table_export()  # host copy of the committed image: the caller's input
     assert image.size <= sfc.STATIC_AREA_BYTES - 256
     st = torch.cuda.current_stream().cuda_stream
