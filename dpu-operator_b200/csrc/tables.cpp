@@ -1219,7 +1219,7 @@ const char* validate_image(const uint8_t* img, size_t len) {
             if (!entry_ok(nodes[i])) return false;
         const LpmTail* tails = (const LpmTail*)(img + tail_off);
         for (uint32_t i = 0; i < ntails; ++i)
-            if (tails[i].len > 128 || tails[i].match == 0 || (tails[i].match & (kLpmChild | kLpmTail)) || (tails[i].fallback & (kLpmChild | kLpmTail)) ||
+            if (tails[i].len < 1 || tails[i].len > 128 || tails[i].match == 0 || (tails[i].match & (kLpmChild | kLpmTail)) || (tails[i].fallback & (kLpmChild | kLpmTail)) ||
                 !value_ok(tails[i].match) || !value_ok(tails[i].fallback))
                 return false;
         return true;
