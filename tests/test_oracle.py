@@ -150,3 +150,32 @@ def test_reference_arm_of_the_bench_loads_no_product_code():
     # and the GPU arm names the same workload (the driver compares the two strings)
     src = open(os.path.join(ROOT, "bench.py")).read()
     assert src.count('"workload": WORKLOAD') == 2
+
+
+def test_bench_stager_numbers_rules_like_the_library():
+    """bench.py's ranks other than 0 stage rules into their oracle without a library handle and must hand out the ids
+    the library hands out on rank 0 (ports, L2 rules, prefixes, ACL rules, flows): run the stager against an offline
+    handle — its asserts compare every id — and check that the handle-less twin ends with the same counts."""
+    import importlib.util
+    import sys
+
+    spec_ = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec_)
+    spec_.loader.exec_module(bench)
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import orc
+
+    with_dp = bench.Stager(sfc.Dataplane(-1), orc, sfc)
+    without = bench.Stager(None, orc, sfc)
+    small = dict(bench.CFG3_SPEC, n_pfx4=600, n_pfx6=200, n_acl=50)
+    for st in (with_dp, without):
+        n_ports = st.chain(8, 4)
+        st.flows(sfc.make_gen_spec(**bench.cfg2_spec_kw(5000, n_ports)), 5000, chunk=2048)
+        st.lpm_acl(sfc.make_gen_spec(**small))
+    with_dp.dp.commit()
+    assert (with_dp.n_ports, with_dp.n_l2, with_dp.n_lpm, with_dp.n_acl, with_dp.n_flows) == \
+           (without.n_ports, without.n_l2, without.n_lpm, without.n_acl, without.n_flows) == (17, 8 * 6 + 5, with_dp.n_lpm, 50, 5000)
+    # and the two oracles answer alike
+    pk = sfc.make_gen_spec(**bench.cfg2_spec_kw(5000, 17))
+    hdr, ports = orc.OracleGen.packets(pk, 0, 20000)
+    assert np.array_equal(with_dp.orc.classify(hdr, ports), without.orc.classify(hdr, ports))
