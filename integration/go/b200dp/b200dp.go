@@ -18,13 +18,30 @@ package b200dp
 import "C"
 import ("errors"; "net"; "strings"; "unsafe")
 
-type B200DP struct{ h *C.sfc_handle }
+// batch > 0: the seven methods stage only; EndBatch makes everything visible with one table commit
+// (one commit per vendor-plugin RPC, as dpu-operator_b200/csrc/host/b200dp.cpp does).
+type B200DP struct {
+	h       *C.sfc_handle
+	batch   int
+	pending bool
+}
 
 func NewB200DP() *B200DP { return &B200DP{} }
 
 func (d *B200DP) err(rc C.int) error {
 	if rc == 0 { return nil }
 	return errors.New(C.GoString(C.sfc_last_error(d.h)))
+}
+func (d *B200DP) commit() error {
+	if d.batch > 0 { d.pending = true; return nil }
+	return d.err(C.sfc_commit(d.h))
+}
+func (d *B200DP) BeginBatch() { d.batch++ }
+func (d *B200DP) EndBatch() error {
+	if d.batch > 0 { d.batch-- }
+	if d.batch > 0 || !d.pending { return nil }
+	d.pending = false
+	return d.err(C.sfc_commit(d.h))
 }
 func (d *B200DP) port(name string) (C.uint16_t, error) {
 	cs := C.CString(name); defer C.free(unsafe.Pointer(cs))
@@ -39,12 +56,12 @@ func (d *B200DP) InitDataPlane(bridgeName string) error {
 func (d *B200DP) AddPortToDataPlane(bridgeName, portName, vfPCIAddres string, isDPDK bool) error {
 	cs := C.CString(portName); defer C.free(unsafe.Pointer(cs))
 	if rc := C.sfc_port_add(d.h, cs, nil); rc != 0 { return d.err(rc) }
-	return d.err(C.sfc_commit(d.h))
+	return d.commit()
 }
 func (d *B200DP) DeletePortFromDataPlane(bridgeName, portName string) error {
 	cs := C.CString(portName); defer C.free(unsafe.Pointer(cs))
 	if rc := C.sfc_port_del(d.h, cs); rc != 0 { return d.err(rc) }
-	return d.err(C.sfc_commit(d.h))
+	return d.commit()
 }
 func (d *B200DP) ReadAllPortFromDataPlane(bridgeName string) (string, error) {
 	n := C.sfc_port_list(d.h, nil, 0)
@@ -62,7 +79,7 @@ func (d *B200DP) AddFlowRuleToDataPlane(bridgeName, inPort, outPort, dstMac stri
 		mac = (*C.uint8_t)(C.CBytes(hw)); defer C.free(unsafe.Pointer(mac))
 	}
 	if rc := C.sfc_l2_rule_add(d.h, in, out, mac, nil); rc != 0 { return d.err(rc) }
-	return d.err(C.sfc_commit(d.h))
+	return d.commit()
 }
 func (d *B200DP) DeleteFlowRuleFromDataPlane(bridgeName, inPort, outPort, dstMac string) error {
 	in, err := d.port(inPort); if err != nil { return err }
@@ -72,6 +89,6 @@ func (d *B200DP) DeleteFlowRuleFromDataPlane(bridgeName, inPort, outPort, dstMac
 		mac = (*C.uint8_t)(C.CBytes(hw)); defer C.free(unsafe.Pointer(mac))
 	}
 	if rc := C.sfc_l2_rule_del(d.h, in, mac); rc != 0 { return d.err(rc) }
-	return d.err(C.sfc_commit(d.h))
+	return d.commit()
 }
 var _ = strings.TrimSpace
